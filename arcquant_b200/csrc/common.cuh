@@ -1,0 +1,84 @@
+// common.cuh -- shared helpers for libarcq_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "arcq.h"
+
+#if defined(__CUDA_ARCH__) && !(__CUDA_ARCH__ >= 1000)
+#error "arcquant_b200 is written for sm_100a only"
+#endif
+
+namespace arcq {
+
+// ---- host-side status plumbing --------------------------------------------------------------
+void set_error(const char *fmt, ...);
+void count_launch(int n = 1);
+int sm_count();  // SMs of the current device (cached), <= 0 on error
+
+#define ARCQ_CUDA_TRY(expr)                                                          \
+  do {                                                                               \
+    cudaError_t e__ = (expr);                                                        \
+    if (e__ != cudaSuccess) {                                                        \
+      arcq::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+      return ARCQ_ECUDA;                                                             \
+    }                                                                                \
+  } while (0)
+
+// ---- numeric conversions (device) -----------------------------------------------------------
+// The arithmetic contract is SURVEY.md Appendix A (reference kernels/src/reorder.cu:127-198).
+
+__device__ __forceinline__ float bf16lo_to_f32(uint32_t packed) { return __uint_as_float(packed << 16); }
+__device__ __forceinline__ float bf16hi_to_f32(uint32_t packed) { return __uint_as_float(packed & 0xffff0000u); }
+
+// E4M3 RNE saturating (== cutlass NumericConverter<float_ue4m3_t,float> on device,
+// third-party/cutlass/include/cutlass/float8.h:1073-1083); input is in [2^-9, 448].
+__device__ __forceinline__ uint32_t f32_to_e4m3(float s) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(0.0f), "f"(s));
+  return (uint32_t)(r & 0xff);
+}
+
+__device__ __forceinline__ float e4m3_to_f32(uint32_t b) {
+  uint32_t h2;
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h2) : "h"((uint16_t)b));
+  return __half2float(__ushort_as_half((unsigned short)(h2 & 0xffff)));
+}
+
+// 8 floats -> 8 e2m1 nibbles packed little-end first (element 0 in the low nibble of byte 0),
+// RNE, saturating at +-6, sign kept on zero.  PTX puts the FIRST source in the HIGH nibble.
+__device__ __forceinline__ uint32_t f32x8_to_e2m1(float a0, float a1, float a2, float a3, float a4,
+                                                  float a5, float a6, float a7) {
+  uint32_t r;
+  asm("{\n\t"
+      ".reg .b8 b0, b1, b2, b3;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b0, %2, %1;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b1, %4, %3;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b2, %6, %5;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b3, %8, %7;\n\t"
+      "mov.b32 %0, {b0, b1, b2, b3};\n\t"
+      "}"
+      : "=r"(r)
+      : "f"(a0), "f"(a1), "f"(a2), "f"(a3), "f"(a4), "f"(a5), "f"(a6), "f"(a7));
+  return r;
+}
+
+// value of one e2m1 code (4 bits, sign | e1 e0 | m): exact.
+__device__ __forceinline__ float e2m1_to_f32(uint32_t c) {
+  // magnitude table {0, .5, 1, 1.5, 2, 3, 4, 6} built arithmetically: no local-memory LUT
+  uint32_t e = (c >> 1) & 3u, m = c & 1u;
+  // e == 0: m * 0.5 ; else (1 + m/2) * 2^(e-1)
+  uint32_t bits = e ? (((126u + e) << 23) | (m << 22)) : (m ? 0x3f000000u : 0u);
+  bits |= (c & 8u) << 28;
+  return __uint_as_float(bits);
+}
+
+__device__ __forceinline__ uint32_t f32_to_bf16_bits(float f) {
+  return (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(f));
+}
+
+}  // namespace arcq
