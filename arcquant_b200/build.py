@@ -71,7 +71,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if p.returncode:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
     tmp = LIB + ".tmp%d" % os.getpid()
-    subprocess.check_call([_nvcc(), "-shared", "-o", tmp] + objs + ["-lcuda"])
+    subprocess.check_call([_nvcc(), "-shared", "-Wno-deprecated-gpu-targets", "-o", tmp] + objs)
     os.replace(tmp, LIB)
     with open(LIB + ".stamp", "w") as f:
         f.write(_fingerprint())

@@ -1,0 +1,324 @@
+// gemm.cu -- NVFP4 block-scaled GEMM on tcgen05 (sm_100a), consuming the augmented K of quant.cu.
+//
+//   D[M,N] bf16 = alpha * sum_k (e2m1(A[m,k]) * e4m3(SFA[m,k/16])) * (e2m1(B[n,k]) * e4m3(SFB[n,k/16]))
+//
+// Replaces the reference's CUTLASS Sm120 mma.sync instantiation (/root/reference/kernels/src/nvfp4.cu:35-132).
+// Hand-written: TMA (cp.async.bulk.tensor, 128-B swizzle) feeds a multi-stage shared-memory ring; scale
+// factors arrive by 1-D bulk copies straight from the swizzled layout the quantise kernel wrote (one
+// 512-B atom per 128 rows x 64 k) and go to TMEM with tcgen05.cp -- no relayout pass anywhere; one
+// elected thread issues tcgen05.mma kind::mxf4nvf4.block_scale (M=128, N=BN, K=64) into TMEM
+// accumulators; four epilogue warps drain TMEM with tcgen05.ld, scale by alpha, round to bf16 and
+// store.  Persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer
+// (+ TMEM allocator), warps 2..5 = epilogue.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace arcq {
+
+constexpr int kBM = 128;         // tile rows (UMMA M)
+constexpr int kBKBytes = 128;    // bytes of packed e2m1 per row per k-block = 256 elements = one swizzle span
+constexpr int kBK = 256;
+constexpr int kGemmThreads = 192;
+
+template <int BN, int STAGES>
+struct GemmCfg {
+  static constexpr int NB = BN / 128;                 // 128-row scale blocks per B tile
+  static constexpr int A_BYTES = kBM * kBKBytes;      // 16 KiB
+  static constexpr int B_BYTES = BN * kBKBytes;
+  static constexpr int SFA_BYTES = 4 * 512;           // 4 k-chunks of one 512-B atom
+  static constexpr int SFB_BYTES = NB * 4 * 512;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + SFA_BYTES + SFB_BYTES;
+  static constexpr int ACC_STAGES = (BN <= 128) ? 2 : 1;
+  static constexpr int SFA_COL = ACC_STAGES * BN;     // TMEM columns: accumulators, then SFA, then SFB
+  static constexpr int SFB_COL = SFA_COL + 16;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static_assert(SFB_COL + 16 * NB <= TMEM_COLS, "TMEM overflow");
+};
+
+struct GemmParams {
+  const uint8_t *sfa;
+  const uint8_t *sfb;
+  __nv_bfloat16 *d;
+  const float *alpha_dev;
+  float alpha;
+  int M, N, K;
+  int tiles_m, tiles_n;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const GemmParams p) {
+  using Cfg = GemmCfg<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t *full = bars;                         // [STAGES]  TMA -> MMA
+  uint64_t *empty = bars + STAGES;               // [STAGES]  MMA -> TMA
+  uint64_t *tfull = bars + 2 * STAGES;           // [ACC]     MMA -> epilogue
+  uint64_t *tempty = tfull + Cfg::ACC_STAGES;    // [ACC]     epilogue -> MMA
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + Cfg::ACC_STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int K = p.K;
+  const int nkb = (K + kBK - 1) / kBK;
+  const int kc_total = K / 64;                   // 64-element chunks (scale atoms) along K
+  const int num_tiles = p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+    for (int a = 0; a < Cfg::ACC_STAGES; ++a) { ptx::mbar_init(&tfull[a], 1); ptx::mbar_init(&tempty[a], 128); }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
+        const int m0 = mt * kBM, n0 = nt * BN;
+        const int nblk_total = (p.N + 127) / 128;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          ptx::mbar_wait(&empty[s], ph ^ 1);
+          uint8_t *st = smem + s * Cfg::STAGE_BYTES;
+          int kchunks = kc_total - kb * 4;
+          if (kchunks > 4) kchunks = 4;
+          int nsfb = nblk_total - nt * Cfg::NB;
+          if (nsfb > Cfg::NB) nsfb = Cfg::NB;
+          const uint32_t sf_bytes = (uint32_t)kchunks * 512u;
+          ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + sf_bytes * (1 + nsfb));
+          ptx::tma_load_2d(st, &tmap_a, kb * kBKBytes, m0, &full[s]);
+          ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, n0, &full[s]);
+          ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)mt * kc_total + kb * 4) * 512, sf_bytes,
+                         &full[s]);
+          for (int j = 0; j < nsfb; ++j)
+            ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + j * 2048,
+                           p.sfb + ((size_t)(nt * Cfg::NB + j) * kc_total + kb * 4) * 512, sf_bytes, &full[s]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_nvfp4(kBM, BN);
+      uint32_t it = 0, tile_it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
+        const int acc = tile_it % Cfg::ACC_STAGES;
+        const uint32_t acc_ph = (tile_it / Cfg::ACC_STAGES) & 1;
+        ptx::mbar_wait(&tempty[acc], acc_ph ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          ptx::mbar_wait(&full[s], ph);
+          ptx::tc_fence_after();
+          uint8_t *st = smem + s * Cfg::STAGE_BYTES;
+          int kchunks = kc_total - kb * 4;
+          if (kchunks > 4) kchunks = 4;
+          const uint32_t a_addr = ptx::smem_u32(st), b_addr = a_addr + Cfg::A_BYTES;
+          const uint32_t sfa_addr = b_addr + Cfg::B_BYTES, sfb_addr = sfa_addr + Cfg::SFA_BYTES;
+          for (int c = 0; c < kchunks; ++c) {
+            ptx::tc_cp_32x128b_warpx4(tmem_base + Cfg::SFA_COL + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
+#pragma unroll
+            for (int j = 0; j < Cfg::NB; ++j)
+              ptx::tc_cp_32x128b_warpx4(tmem_base + Cfg::SFB_COL + c * 4 * Cfg::NB + j * 4,
+                                        ptx::make_sf_desc(sfb_addr + j * 2048 + c * 512));
+          }
+          const uint64_t a_desc = ptx::make_sw128_kmajor_desc(a_addr);
+          const uint64_t b_desc = ptx::make_sw128_kmajor_desc(b_addr);
+          for (int c = 0; c < kchunks; ++c) {
+            // advance 32 bytes (64 e2m1) inside the 128-B swizzle span: +2 in the 16-B address field
+            ptx::tc_mma_nvfp4(d_tmem, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
+                              tmem_base + Cfg::SFA_COL + c * 4, tmem_base + Cfg::SFB_COL + c * 4 * Cfg::NB);
+          }
+          ptx::tc_commit(&empty[s]);  // frees the smem stage once these MMAs have read it
+        }
+        ptx::tc_commit(&tfull[acc]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    float alpha = p.alpha;
+    if (p.alpha_dev) alpha = __ldg(p.alpha_dev);
+    uint32_t tile_it = 0;
+    const bool vec_ok = (p.N % 8) == 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
+      const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
+      const int acc = tile_it % Cfg::ACC_STAGES;
+      const uint32_t acc_ph = (tile_it / Cfg::ACC_STAGES) & 1;
+      ptx::mbar_wait(&tfull[acc], acc_ph);
+      ptx::tc_fence_after();
+      const int row = mt * kBM + q * 32 + lane;
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+      __nv_bfloat16 *drow = p.d + (size_t)row * p.N;
+#pragma unroll 1
+      for (int cb = 0; cb < BN / 32; ++cb) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r);
+        ptx::tmem_ld_wait();
+        const int col0 = nt * BN + cb * 32;
+        if (row < p.M && col0 < p.N) {
+          if (vec_ok && col0 + 32 <= p.N) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(alpha * __uint_as_float(r[8 * v + 2 * e]),
+                                                         alpha * __uint_as_float(r[8 * v + 2 * e + 1]));
+                o[e] = *reinterpret_cast<uint32_t *>(&h);
+              }
+              *reinterpret_cast<uint4 *>(drow + col0 + 8 * v) = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (col0 + e < p.N) drow[col0 + e] = __float2bfloat16_rn(alpha * __uint_as_float(r[e]));
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&tempty[acc]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---- host side ------------------------------------------------------------------------------
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)sym;
+  });
+  return fn;
+}
+
+// 2-D map over a row-major u8 matrix [rows, row_bytes]; box = 128 bytes x box_rows, 128-B swizzle,
+// out-of-bounds reads (row tails, K tail) return zeros.
+static int make_operand_map(CUtensorMap *map, const void *ptr, int64_t rows, int64_t row_bytes, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return ARCQ_ECUDA; }
+  cuuint64_t dims[2] = {(cuuint64_t)row_bytes, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)row_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)kBKBytes, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return ARCQ_ECUDA; }
+  return ARCQ_OK;
+}
+
+struct MapKey {
+  const void *ptr; int64_t rows, row_bytes; int box_rows;
+  bool operator==(const MapKey &o) const { return ptr == o.ptr && rows == o.rows && row_bytes == o.row_bytes && box_rows == o.box_rows; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey &k) const {
+    return std::hash<const void *>()(k.ptr) ^ (std::hash<int64_t>()(k.rows) * 31) ^ (std::hash<int64_t>()(k.row_bytes) * 131) ^ k.box_rows;
+  }
+};
+
+// Encoding a tensor map costs a few microseconds of host time; weights (and CUDA-graph-stable
+// activation buffers) come back with the same (pointer, shape), so keep them.
+static int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t row_bytes, int box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  MapKey key{ptr, rows, row_bytes, box_rows};
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return ARCQ_OK; }
+  if (int rc = make_operand_map(out, ptr, rows, row_bytes, box_rows)) return rc;
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, *out);
+  return ARCQ_OK;
+}
+
+template <int BN, int STAGES>
+static int launch_gemm(const void *a, const void *b, GemmParams p, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN, STAGES>;
+  auto kern = gemm_nvfp4_kernel<BN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  CUtensorMap ta, tb;
+  if (int rc = cached_operand_map(&ta, a, p.M, p.K / 2, kBM)) return rc;
+  if (int rc = cached_operand_map(&tb, b, p.N, p.K / 2, BN)) return rc;
+  p.tiles_m = (p.M + kBM - 1) / kBM;
+  p.tiles_n = (p.N + BN - 1) / BN;
+  const int sms = sm_count();
+  if (sms <= 0) return ARCQ_ECUDA;
+  int grid = p.tiles_m * p.tiles_n;
+  if (grid > sms) grid = sms;
+  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  ARCQ_CUDA_TRY(cudaGetLastError());
+  count_launch();
+  return ARCQ_OK;
+}
+
+}  // namespace arcq
+
+using namespace arcq;
+
+extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
+                               int64_t K, float alpha, const float *alpha_dev, void *d, void *stream) {
+  if (!a || !b || !sfa || !sfb || !d) { set_error("null pointer argument"); return ARCQ_EINVAL; }
+  if (M < 0 || N < 0 || M > 0x7fffff00 || N > 0x7fffff00) { set_error("M/N out of range"); return ARCQ_EINVAL; }
+  if (K <= 0 || K % 64 || K > (1 << 20)) { set_error("K=%lld must be a positive multiple of 64", (long long)K); return ARCQ_EINVAL; }
+  if (((uintptr_t)a | (uintptr_t)b | (uintptr_t)sfa | (uintptr_t)sfb | (uintptr_t)d) & 15) {
+    set_error("pointers must be 16-byte aligned");
+    return ARCQ_EINVAL;
+  }
+  if (M == 0 || N == 0) return ARCQ_OK;
+  GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, alpha, (int)M, (int)N, (int)K, 0, 0};
+  cudaStream_t st = (cudaStream_t)stream;
+  static int forced_bn = -1;
+  if (forced_bn < 0) {
+    const char *e = getenv("ARCQ_GEMM_BN");
+    forced_bn = e ? atoi(e) : 0;
+  }
+  int bn = forced_bn;
+  if (bn != 128 && bn != 256) {
+    // wide tiles halve A re-reads and MMA issue count; narrow tiles fill the SMs for small problems
+    const int64_t tiles256 = ((M + kBM - 1) / kBM) * ((N + 255) / 256);
+    bn = (tiles256 >= 2 * (int64_t)sm_count() || N % 256 == 0) && N > 128 ? 256 : 128;
+  }
+  if (bn == 256) return launch_gemm<256, 4>(a, b, p, st);
+  return launch_gemm<128, 6>(a, b, p, st);
+}
