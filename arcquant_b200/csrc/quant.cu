@@ -318,8 +318,8 @@ static int pick_rows(int KQ, int KE, bool rms) {
 
 static int check_common(const void *x, int64_t M, int KQ, const void *idx, int KE, int flavour, const void *q,
                         const void *sf) {
-  if (!x || !idx || !q || !sf) { set_error("null pointer argument"); return ARCQ_EINVAL; }
   if (M < 0 || M > 0x7fffff00) { set_error("row count %lld out of range", (long long)M); return ARCQ_EINVAL; }
+  if (!idx || !sf || (M > 0 && (!x || !q))) { set_error("null pointer argument"); return ARCQ_EINVAL; }
   const int w = flavour == ARCQ_FLAVOUR_32 ? 32 : 16;
   if (KQ <= 0 || KQ > 32768 || KE < 0 || KE > KQ || KQ % w || KE % w || (KQ + KE) % 64) {
     set_error("unsupported shape KQ=%d KE=%d for the %d-wide flavour (need KQ%%%d==0, KE%%%d==0, (KQ+KE)%%64==0, KE<=KQ<=32768)",

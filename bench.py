@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""bench.py -- NVFP4+ARC hot path on B200: quantise (reorder + NVFP4 + ARC) + block-scaled GEMM.
+
+A "step" is one pass of the hot path over one batch of M synthetic tokens through the seven linears of
+one Llama-3-8B decoder layer, called exactly as the reference's layers call `agemm`
+(model/qLlamaLayer.py:296-303,364-367,429-443): 4 quantise launches + 7 GEMM launches.
+`value` = useful GEMM FLOPs (2*M*N*(KQ+KE), ARC columns included) of the step / device time of the whole
+step (quantise kernels included), inputs resident in HBM.  `e2e` = same metric through the public
+`agemm` API with HOST (pinned) activations copied in and results copied out inside the timed region.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--tokens M] [--impl native|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# (name, KQ, KE, [N of each GEMM that shares this quantised activation]) -- Llama-3-8B, SURVEY.md App. B
+LLAMA3_8B_LAYER = [
+    ("qkv", 4096, 256, [4096, 1024, 1024]),
+    ("o", 4096, 256, [4096]),
+    ("gate_up", 4096, 256, [14336, 14336]),
+    ("down", 14336, 512, [4096]),
+]
+
+
+def layer_flops(M):
+    return sum(2.0 * M * n * (kq + ke) for _, kq, ke, ns in LLAMA3_8B_LAYER for n in ns)
+
+
+def quant_bytes(M, KQ, KE):
+    """Algorithmic bytes of one quantise launch: bf16 row in, codes + scales out, index once."""
+    return M * (2 * KQ + (KQ + KE) // 2 + (KQ + KE) // 16) + 2 * KQ
+
+
+def gemm_bytes(M, N, K):
+    return 0.5625 * K * (M + N) + 2.0 * M * N
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [c.strip() for c in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_fakequant_step(M, torch, fq, state):
+    """One bounded CPU sample: the reference's fake-quant linear (model/quantize.py path) for the q_proj shape."""
+    x, w, idx, KE = state
+    t0 = time.perf_counter()
+    y = fq.fake_linear(x[:M], w, idx, KE)
+    dt = time.perf_counter() - t0
+    return dt, y
+
+
+def make_cpu_state(torch, M):
+    from tests._util import make_acts
+    KQ, KE, N = 4096, 256, 4096
+    x, idx = make_acts(M, KQ, KE, seed=0)
+    g = torch.Generator().manual_seed(1)
+    w = (torch.randn(N, KQ, generator=g) * 0.02).to(torch.bfloat16)
+    return (x.float(), w.float(), idx.long(), KE), (KQ, KE, N)
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path (PyTorch fake-quant,
+    restated in oracle/fakequant.py because /root/reference does not travel) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from oracle import fakequant as fq
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    M = args.cpu_tokens
+    state, (KQ, KE, N) = make_cpu_state(torch, M)
+    for _ in range(max(1, min(args.warmup, 2))):
+        cpu_fakequant_step(M, torch, fq, state)
+    ts = [cpu_fakequant_step(M, torch, fq, state)[0] for _ in range(args.steps)]
+    total = sum(ts)
+    flops = 2.0 * M * N * (KQ + KE)
+    val = flops * len(ts) / total / 1e12
+    sample = "fake-quant linear (quantize x + quantize w + F.linear) M=%d, 4096x4096, KE=256, fp32 on CPU" % M
+    print(json.dumps({
+        "impl": "reference", "metric": "nvfp4_arc_linear_tflops", "value": val, "unit": "TFLOP/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(ts), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "nvfp4 (e2m1 x e2m1, ue4m3 block scales, fp32 accumulate)",
+        "data": "synthetic",
+        "config": {"workload": "llama3-8b decoder-layer linears, NVFP4+ARC quantize + GEMM", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+class Layer:
+    """Device-resident state of one Llama-3-8B layer's linears: quantised weights + activation buffers."""
+
+    def __init__(self, torch, agemm, M, dev, seed=0):
+        from tests._util import make_acts
+        self.torch, self.agemm, self.M = torch, agemm, M
+        self.items = []
+        g = torch.Generator().manual_seed(seed)
+        for name, KQ, KE, Ns in LLAMA3_8B_LAYER:
+            xs, idx = make_acts(min(M, 256), KQ, KE, seed=seed + KQ)  # distribution A, pre-scaled
+            reps = (M + xs.shape[0] - 1) // xs.shape[0]
+            x_host = xs.repeat(reps, 1)[:M].contiguous()
+            # de-correlate repeated blocks cheaply: flip signs per row block
+            sign = (torch.randint(0, 2, (M, 1), generator=g) * 2 - 1).to(torch.bfloat16)
+            x_host = (x_host * sign).contiguous().pin_memory()
+            idx_d = idx.to(dev)
+            ws = []
+            for N in Ns:
+                w = (torch.randn(N, KQ, generator=g) * 0.02).to(torch.bfloat16)
+                sw = w.max().float() / (448.0 * 6.0)
+                qw, sfw = agemm.reorder_quantize_w((w / sw).to(torch.bfloat16).to(dev), idx_d, KE)
+                ws.append((N, qw, sfw, float(sw)))
+            self.items.append({"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host,
+                               "x": x_host.to(dev), "w": ws,
+                               "y": [torch.empty((M, N), dtype=torch.bfloat16, device=dev) for N in Ns],
+                               "y_host": [torch.empty((M, N), dtype=torch.bfloat16).pin_memory() for N in Ns]})
+        torch.cuda.synchronize()
+
+    def step(self, events=None):
+        """4 quantise + 7 GEMM launches, inputs resident in HBM."""
+        ag = self.agemm
+        for it in self.items:
+            if events is not None:
+                e0 = self.torch.cuda.Event(enable_timing=True); e0.record()
+            qx, sfx = ag.reorder_quantize_x(it["x"], it["idx"], it["KE"])
+            if events is not None:
+                e1 = self.torch.cuda.Event(enable_timing=True); e1.record()
+                events.append(("quant", it["KQ"], it["KE"], 0, e0, e1))
+            for (N, qw, sfw, sw), y in zip(it["w"], it["y"]):
+                if events is not None:
+                    e0 = self.torch.cuda.Event(enable_timing=True); e0.record()
+                ag.matmul(qx, qw, sfx, sfw, sw, out=y)
+                if events is not None:
+                    e1 = self.torch.cuda.Event(enable_timing=True); e1.record()
+                    events.append(("gemm", it["KQ"], it["KE"], N, e0, e1))
+
+    def step_e2e(self):
+        """Same step through the public API with host buffers: H2D of every activation, D2H of every result."""
+        ag = self.agemm
+        for it in self.items:
+            x = it["x_host"].to(it["x"].device, non_blocking=True)
+            qx, sfx = ag.reorder_quantize_x(x, it["idx"], it["KE"])
+            for (N, qw, sfw, sw), y, yh in zip(it["w"], it["y"], it["y_host"]):
+                ag.matmul(qx, qw, sfx, sfw, sw, out=y)
+                yh.copy_(y, non_blocking=True)
+
+    def e2e_bytes(self):
+        h2d = sum(it["x_host"].numel() * 2 for it in self.items)
+        d2h = sum(y.numel() * 2 for it in self.items for y in it["y_host"])
+        return h2d, d2h
+
+
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from arcquant_b200 import agemm
+    peaks = load_peaks()
+    M = args.tokens
+    layer = Layer(torch, agemm, M, dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        layer.step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = agemm.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        layer.step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = agemm.launch_count() - n0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    flops = layer_flops(M)
+    value = world * flops * args.steps / (ms_max * 1e-3) / 1e12
+
+    # ---- e2e: host activations in, results out, inside the timed region ----
+    for _ in range(2):
+        layer.step_e2e()
+    barrier()
+    e0.record()
+    for _ in range(args.e2e_steps):
+        layer.step_e2e()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = world * flops * args.e2e_steps / (float(t.item()) * 1e-3) / 1e12
+    h2d, d2h = layer.e2e_bytes()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel averages (instrumented pass: CUDA events around every launch, same stream) ----
+    events = []
+    for _ in range(args.steps):
+        layer.step(events)
+    torch.cuda.synchronize()
+    per = {}
+    for kind, KQ, KE, N, a, b in events:
+        per.setdefault((kind, KQ, KE, N), []).append(a.elapsed_time(b))
+    kernels = []
+    total_ms = 0.0
+    for (kind, KQ, KE, N), v in sorted(per.items()):
+        avg = sum(v) / len(v)
+        calls_per_step = len(v) / args.steps
+        total_ms += avg * calls_per_step
+        if kind == "quant":
+            by = quant_bytes(M, KQ, KE)
+            kernels.append({"kernel": "quant", "KQ": KQ, "KE": KE, "us": 1e3 * avg, "calls_per_step": calls_per_step,
+                            "GBps": by / (avg * 1e-3) / 1e9, "frac_hbm": by / (avg * 1e-3) / 1e9 / peaks["hbm_gbs"]})
+        else:
+            fl = 2.0 * M * N * (KQ + KE)
+            kernels.append({"kernel": "gemm", "N": N, "K": KQ + KE, "us": 1e3 * avg, "calls_per_step": calls_per_step,
+                            "TFLOPs": fl / (avg * 1e-3) / 1e12})
+    gemms = [k for k in kernels if k["kernel"] == "gemm"]
+    dom = max(gemms, key=lambda k: k["us"] * k["calls_per_step"])
+    nvfp4_peak = 4.0 * peaks["bf16_tflops"]
+    roofline = {"bound": "tensor", "kernel": "gemm_nvfp4_kernel N=%d K=%d M=%d" % (dom["N"], dom["K"], M),
+                "achieved": dom["TFLOPs"], "peak": nvfp4_peak, "unit": "TFLOP/s", "frac": dom["TFLOPs"] / nvfp4_peak,
+                "peak_basis": "4 x %s cuBLAS bf16 burst (%.1f TF/s) from MEASURED_PEAKS.json; nominal dense NVFP4 is 9000"
+                              % (peaks["source"], peaks["bf16_tflops"]),
+                "frac_of_nominal_9000": dom["TFLOPs"] / 9000.0, "traffic": None,
+                "share_of_step": dom["us"] * dom["calls_per_step"] / (1e3 * total_ms)}
+    qk = max([k for k in kernels if k["kernel"] == "quant"], key=lambda k: k["us"])
+    roofline_quant = {"bound": "hbm", "kernel": "quant_kernel KQ=%d KE=%d M=%d" % (qk["KQ"], qk["KE"], M),
+                      "achieved": qk["GBps"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": qk["frac_hbm"],
+                      "peak_basis": "%s copy bandwidth" % peaks["source"], "traffic": None}
+
+    # ---- CPU baseline on this box's host cores (bounded sample) ----
+    cpu = None
+    if not args.no_cpu_baseline:
+        from oracle import fakequant as fq
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        Mc = args.cpu_tokens
+        state, (KQ, KE, N) = make_cpu_state(torch, Mc)
+        cpu_fakequant_step(Mc, torch, fq, state)
+        ts = [cpu_fakequant_step(Mc, torch, fq, state)[0] for _ in range(args.cpu_reps)]
+        cpu = {"value": 2.0 * Mc * N * (KQ + KE) * len(ts) / sum(ts) / 1e12, "unit": "TFLOP/s", "cores": cores,
+               "kind": "port",
+               "sample": "%d x fake-quant linear (model/quantize.py path restated in oracle/fakequant.py) M=%d, "
+                         "4096x4096, KE=256, fp32; %.1f s of CPU work" % (len(ts), Mc, sum(ts))}
+
+    out = {
+        "metric": "nvfp4_arc_linear_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "nvfp4 (e2m1 x e2m1, ue4m3 block scales, fp32 accumulate, bf16 out)",
+        "data": "synthetic",
+        "config": {"workload": "llama3-8b decoder-layer linears (qkv, o, gate/up, down): 4 x reorder+NVFP4+ARC quantize "
+                               "+ 7 x block-scaled GEMM per step", "tokens_per_gpu": M,
+                   "select_num": {n: ke for n, _, ke, _ in LLAMA3_8B_LAYER},
+                   "l2": "inputs larger than L2 (per-step working set > 1 GB vs 126 MB L2); no flush needed",
+                   "parallelism": "replicas (token-parallel), no collective" if world > 1 else "single GPU"},
+        "tokens_per_s_linear_path": world * M * args.steps / (ms_max * 1e-3),
+        "e2e": {"value": e2e_val, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "steps": args.e2e_steps},
+        "gpu_launches": int(launches),
+        "roofline": roofline, "roofline_quant": roofline_quant, "kernels": kernels,
+        "cpu_baseline": cpu, "clocks": clocks,
+    }
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--tokens", type=int, default=8192, help="M: rows (tokens) per GPU per step")
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-tokens", type=int, default=512)
+    ap.add_argument("--cpu-reps", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()
