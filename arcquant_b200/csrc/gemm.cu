@@ -255,7 +255,7 @@ struct MapKeyHash {
 
 // Encoding a tensor map costs a few microseconds of host time; weights (and CUDA-graph-stable
 // activation buffers) come back with the same (pointer, shape), so keep them.
-static int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t row_bytes, int box_rows) {
+int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t row_bytes, int box_rows) {
   static std::mutex mu;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   MapKey key{ptr, rows, row_bytes, box_rows};
@@ -296,6 +296,12 @@ static int launch_gemm(const void *a, const void *b, GemmParams p, cudaStream_t 
 
 using namespace arcq;
 
+namespace arcq {
+int launch_gemm_cluster(int shape, const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K,
+                        float alpha, const float *alpha_dev, void *d, cudaStream_t stream);
+}
+static const int kDefaultClusterShape = 0;  // set once the cluster kernel is validated on hardware
+
 extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
                                int64_t K, float alpha, const float *alpha_dev, void *d, void *stream) {
   if (!a || !b || !sfa || !sfb || !d) { set_error("null pointer argument"); return ARCQ_EINVAL; }
@@ -308,15 +314,18 @@ extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, co
   if (M == 0 || N == 0) return ARCQ_OK;
   GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, alpha, (int)M, (int)N, (int)K, 0, 0};
   cudaStream_t st = (cudaStream_t)stream;
-  static int forced_bn = -1;
-  if (forced_bn < 0) {
-    const char *e = getenv("ARCQ_GEMM_BN");
-    forced_bn = e ? atoi(e) : 0;
-  }
-  int bn = forced_bn;
+  // ARCQ_GEMM_CLUSTER=<10*CM+CN> forces a multicast cluster shape (0 = never), ARCQ_GEMM_BN forces the tile
+  // width of the non-cluster kernel; both are for experiments, the defaults below are the tuned choice.
+  const char *ec = getenv("ARCQ_GEMM_CLUSTER");
+  int cshape = ec ? atoi(ec) : -1;
+  const int64_t tiles256 = ((M + kBM - 1) / kBM) * ((N + 255) / 256);
+  if (cshape < 0) cshape = tiles256 >= 2 * (int64_t)sm_count() ? kDefaultClusterShape : 0;
+  if (cshape > 0)
+    return launch_gemm_cluster(cshape, a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, d, st);
+  const char *e = getenv("ARCQ_GEMM_BN");
+  int bn = e ? atoi(e) : 0;
   if (bn != 128 && bn != 256) {
     // wide tiles halve A re-reads and MMA issue count; narrow tiles fill the SMs for small problems
-    const int64_t tiles256 = ((M + kBM - 1) / kBM) * ((N + 255) / 256);
     bn = (tiles256 >= 2 * (int64_t)sm_count() || N % 256 == 0) && N > 128 ? 256 : 128;
   }
   if (bn == 256) return launch_gemm<256, 4>(a, b, p, st);
