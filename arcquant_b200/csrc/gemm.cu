@@ -7,9 +7,16 @@
 // factors arrive by 1-D bulk copies straight from the swizzled layout the quantise kernel wrote (one
 // 512-B atom per 128 rows x 64 k) and go to TMEM with tcgen05.cp -- no relayout pass anywhere; one
 // elected thread issues tcgen05.mma kind::mxf4nvf4.block_scale (M=128, N=BN, K=64) into TMEM
-// accumulators; four epilogue warps drain TMEM with tcgen05.ld, scale by alpha, round to bf16 and
-// store.  Persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer
-// (+ TMEM allocator), warps 2..5 = epilogue.
+// accumulators.  Persistent CTAs (one per SM), warp-specialised: warp 0 = TMA producer, warp 1 = MMA
+// issuer (+ TMEM allocator), warps 2..9 = epilogue.
+//
+// Measured design points (profiles/r1_gemm_notes.md):
+//  * tcgen05.cp writes TMEM at ~64 B/clk and the x4 lane-quadrant replication makes the scale factors of a
+//    128x256x256 k-block 24 KB of TMEM writes (~390 clk next to 512 clk of MMA) -> the scale-factor TMEM
+//    region is double-buffered so the copies of k-block i+1 are not ordered behind the MMAs of k-block i;
+//  * the epilogue pulls the whole accumulator into registers, releases TMEM at once (the next tile's MMAs
+//    start while bf16 conversion and stores run) and stores through an XOR-swizzled shared staging buffer so
+//    every global store instruction writes whole 128-byte lines.
 #include <cuda.h>
 
 #include <mutex>
@@ -23,7 +30,8 @@ namespace arcq {
 constexpr int kBM = 128;         // tile rows (UMMA M)
 constexpr int kBKBytes = 128;    // bytes of packed e2m1 per row per k-block = 256 elements = one swizzle span
 constexpr int kBK = 256;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;
+constexpr int kEpiWarps = 8;
 
 template <int BN, int STAGES>
 struct GemmCfg {
@@ -34,11 +42,13 @@ struct GemmCfg {
   static constexpr int SFB_BYTES = NB * 4 * 512;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + SFA_BYTES + SFB_BYTES;
   static constexpr int ACC_STAGES = (BN <= 128) ? 2 : 1;
-  static constexpr int SFA_COL = ACC_STAGES * BN;     // TMEM columns: accumulators, then SFA, then SFB
-  static constexpr int SFB_COL = SFA_COL + 16;
+  static constexpr int SF_COLS = 16 + 16 * NB;        // one scale-factor buffer: SFA (16 cols) then SFB
+  static constexpr int SF_COL0 = ACC_STAGES * BN;     // TMEM columns: accumulators, then 2 scale-factor buffers
   static constexpr int TMEM_COLS = 512;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-  static_assert(SFB_COL + 16 * NB <= TMEM_COLS, "TMEM overflow");
+  static constexpr int EPI_BYTES = kEpiWarps * 4096;  // per-warp 32 rows x 128 B staging
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static_assert(SF_COL0 + 2 * SF_COLS <= TMEM_COLS, "TMEM overflow");
+  static_assert(SMEM_BYTES <= 232448, "shared memory overflow");
 };
 
 struct GemmParams {
@@ -49,6 +59,7 @@ struct GemmParams {
   float alpha;
   int M, N, K;
   int tiles_m, tiles_n;
+  int debug;  // experiments only: bit0 = skip TMA loads, bit1 = skip MMA issue, bit2 = skip UTCCP, bit3 = skip stores
 };
 
 template <int BN, int STAGES>
@@ -58,7 +69,8 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   using Cfg = GemmCfg<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint8_t *epi = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(epi + Cfg::EPI_BYTES);
   uint64_t *full = bars;                         // [STAGES]  TMA -> MMA
   uint64_t *empty = bars + STAGES;               // [STAGES]  MMA -> TMA
   uint64_t *tfull = bars + 2 * STAGES;           // [ACC]     MMA -> epilogue
@@ -75,7 +87,7 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     ptx::prefetch_tmap(&tmap_a);
     ptx::prefetch_tmap(&tmap_b);
     for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
-    for (int a = 0; a < Cfg::ACC_STAGES; ++a) { ptx::mbar_init(&tfull[a], 1); ptx::mbar_init(&tempty[a], 128); }
+    for (int a = 0; a < Cfg::ACC_STAGES; ++a) { ptx::mbar_init(&tfull[a], 1); ptx::mbar_init(&tempty[a], kEpiWarps); }
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -91,10 +103,12 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t it = 0;
+      const int nblk_total = (p.N + 127) / 128;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
         const int m0 = mt * kBM, n0 = nt * BN;
-        const int nblk_total = (p.N + 127) / 128;
+        int nsfb = nblk_total - nt * Cfg::NB;
+        if (nsfb > Cfg::NB) nsfb = Cfg::NB;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
@@ -102,9 +116,8 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           uint8_t *st = smem + s * Cfg::STAGE_BYTES;
           int kchunks = kc_total - kb * 4;
           if (kchunks > 4) kchunks = 4;
-          int nsfb = nblk_total - nt * Cfg::NB;
-          if (nsfb > Cfg::NB) nsfb = Cfg::NB;
           const uint32_t sf_bytes = (uint32_t)kchunks * 512u;
+          if (p.debug & 1) { ptx::mbar_arrive(&full[s]); continue; }
           ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + sf_bytes * (1 + nsfb));
           ptx::tma_load_2d(st, &tmap_a, kb * kBKBytes, m0, &full[s]);
           ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, n0, &full[s]);
@@ -137,19 +150,20 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (kchunks > 4) kchunks = 4;
           const uint32_t a_addr = ptx::smem_u32(st), b_addr = a_addr + Cfg::A_BYTES;
           const uint32_t sfa_addr = b_addr + Cfg::B_BYTES, sfb_addr = sfa_addr + Cfg::SFA_BYTES;
-          for (int c = 0; c < kchunks; ++c) {
-            ptx::tc_cp_32x128b_warpx4(tmem_base + Cfg::SFA_COL + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
-#pragma unroll
-            for (int j = 0; j < Cfg::NB; ++j)
-              ptx::tc_cp_32x128b_warpx4(tmem_base + Cfg::SFB_COL + c * 4 * Cfg::NB + j * 4,
-                                        ptx::make_sf_desc(sfb_addr + j * 2048 + c * 512));
-          }
+          const uint32_t sfa_t = tmem_base + Cfg::SF_COL0 + (it & 1) * Cfg::SF_COLS, sfb_t = sfa_t + 16;
           const uint64_t a_desc = ptx::make_sw128_kmajor_desc(a_addr);
           const uint64_t b_desc = ptx::make_sw128_kmajor_desc(b_addr);
           for (int c = 0; c < kchunks; ++c) {
+            if (!(p.debug & 4)) {
+              ptx::tc_cp_32x128b_warpx4(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
+#pragma unroll
+              for (int j = 0; j < Cfg::NB; ++j)
+                ptx::tc_cp_32x128b_warpx4(sfb_t + c * 4 * Cfg::NB + j * 4, ptx::make_sf_desc(sfb_addr + j * 2048 + c * 512));
+            }
             // advance 32 bytes (64 e2m1) inside the 128-B swizzle span: +2 in the 16-B address field
-            ptx::tc_mma_nvfp4(d_tmem, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
-                              tmem_base + Cfg::SFA_COL + c * 4, tmem_base + Cfg::SFB_COL + c * 4 * Cfg::NB);
+            if (!(p.debug & 2))
+              ptx::tc_mma_nvfp4(d_tmem, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
+                                sfa_t + c * 4, sfb_t + c * 4 * Cfg::NB);
           }
           ptx::tc_commit(&empty[s]);  // frees the smem stage once these MMAs have read it
         }
@@ -157,49 +171,66 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    // ===================== epilogue (warps 2..9): lane quadrant = warp % 4, column half = (warp - 2) / 4 ======
+    constexpr int HC = BN / 2;   // columns per warp
+    const int q = warp & 3, half = (warp - 2) >> 2;
     float alpha = p.alpha;
     if (p.alpha_dev) alpha = __ldg(p.alpha_dev);
-    uint32_t tile_it = 0;
+    uint8_t *wst = epi + (warp - 2) * 4096;
     const bool vec_ok = (p.N % 8) == 0;
+    uint32_t tile_it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
       const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
       const int acc = tile_it % Cfg::ACC_STAGES;
       const uint32_t acc_ph = (tile_it / Cfg::ACC_STAGES) & 1;
       ptx::mbar_wait(&tfull[acc], acc_ph);
       ptx::tc_fence_after();
-      const int row = mt * kBM + q * 32 + lane;
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-      __nv_bfloat16 *drow = p.d + (size_t)row * p.N;
-#pragma unroll 1
-      for (int cb = 0; cb < BN / 32; ++cb) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r);
-        ptx::tmem_ld_wait();
-        const int col0 = nt * BN + cb * 32;
-        if (row < p.M && col0 < p.N) {
-          if (vec_ok && col0 + 32 <= p.N) {
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + half * HC;
+      uint32_t r[HC / 32][32];
 #pragma unroll
-            for (int v = 0; v < 4; ++v) {
-              uint32_t o[4];
+      for (int cb = 0; cb < HC / 32; ++cb) ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r[cb]);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tempty[acc]);  // accumulator is in registers: the next MMAs may start
+      if (p.debug & 8) continue;
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                __nv_bfloat162 h = __floats2bfloat162_rn(alpha * __uint_as_float(r[8 * v + 2 * e]),
-                                                         alpha * __uint_as_float(r[8 * v + 2 * e + 1]));
-                o[e] = *reinterpret_cast<uint32_t *>(&h);
-              }
-              *reinterpret_cast<uint4 *>(drow + col0 + 8 * v) = make_uint4(o[0], o[1], o[2], o[3]);
+      for (int pass = 0; pass < HC / 64; ++pass) {
+        // lane = row: 64 columns -> 8 chunks of 8 bf16, chunk j at swizzled slot j ^ (row & 7)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int col = pass * 64 + j * 8 + 2 * e;
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(alpha * __uint_as_float(r[col >> 5][col & 31]),
+                                                      alpha * __uint_as_float(r[col >> 5][(col & 31) + 1]));
+            o[e] = *reinterpret_cast<uint32_t *>(&h2);
+          }
+          *reinterpret_cast<uint4 *>(wst + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+        __syncwarp();
+        const int j = lane & 7;
+        const int gcol = nt * BN + half * HC + pass * 64 + j * 8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = i * 4 + (lane >> 3);
+          const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * 128 + ((j ^ (rr & 7)) << 4));
+          const int grow = mt * kBM + q * 32 + rr;
+          if (grow < p.M && gcol < p.N) {
+            __nv_bfloat16 *dst = p.d + (size_t)grow * p.N + gcol;
+            if (vec_ok && gcol + 8 <= p.N) {
+              *reinterpret_cast<uint4 *>(dst) = v;
+            } else {
+              const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                if (gcol + e < p.N) dst[e] = __ushort_as_bfloat16((unsigned short)(w[e >> 1] >> (16 * (e & 1))));
             }
-          } else {
-#pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (col0 + e < p.N) drow[col0 + e] = __float2bfloat16_rn(alpha * __uint_as_float(r[e]));
           }
         }
+        __syncwarp();
       }
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(&tempty[acc]);
     }
   }
 
@@ -312,7 +343,8 @@ extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, co
     return ARCQ_EINVAL;
   }
   if (M == 0 || N == 0) return ARCQ_OK;
-  GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, alpha, (int)M, (int)N, (int)K, 0, 0};
+  GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, alpha, (int)M, (int)N, (int)K, 0, 0, 0};
+  if (const char *dbg = getenv("ARCQ_GEMM_DEBUG")) p.debug = atoi(dbg);
   cudaStream_t st = (cudaStream_t)stream;
   // ARCQ_GEMM_CLUSTER=<10*CM+CN> forces a multicast cluster shape (0 = never), ARCQ_GEMM_BN forces the tile
   // width of the non-cluster kernel; both are for experiments, the defaults below are the tuned choice.
@@ -328,6 +360,6 @@ extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, co
     // wide tiles halve A re-reads and MMA issue count; narrow tiles fill the SMs for small problems
     bn = (tiles256 >= 2 * (int64_t)sm_count() || N % 256 == 0) && N > 128 ? 256 : 128;
   }
-  if (bn == 256) return launch_gemm<256, 4>(a, b, p, st);
-  return launch_gemm<128, 6>(a, b, p, st);
+  if (bn == 256) return launch_gemm<256, 3>(a, b, p, st);
+  return launch_gemm<128, 5>(a, b, p, st);
 }
