@@ -101,7 +101,10 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    // The whole warp runs the loop and the barrier waits; only the elect.sync leader issues.  (Issuing from
+    // inside an `if (lane == 0)` branch makes ptxas wrap every uniform-datapath instruction -- UTMALDG,
+    // UTCCP, UTCOMMA, UTCBAR -- in an ELECT/R2UR.BROADCAST waterfall loop: ~45 ns per instruction measured.)
+    {
       uint32_t it = 0;
       const int nblk_total = (p.N + 127) / 128;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -117,21 +120,27 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           int kchunks = kc_total - kb * 4;
           if (kchunks > 4) kchunks = 4;
           const uint32_t sf_bytes = (uint32_t)kchunks * 512u;
-          if (p.debug & 1) { ptx::mbar_arrive(&full[s]); continue; }
-          ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + sf_bytes * (1 + nsfb));
-          ptx::tma_load_2d(st, &tmap_a, kb * kBKBytes, m0, &full[s]);
-          ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, n0, &full[s]);
-          ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)mt * kc_total + kb * 4) * 512, sf_bytes,
-                         &full[s]);
-          for (int j = 0; j < nsfb; ++j)
-            ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + j * 2048,
-                           p.sfb + ((size_t)(nt * Cfg::NB + j) * kc_total + kb * 4) * 512, sf_bytes, &full[s]);
+          if (ptx::elect_one()) {
+            if (p.debug & 1) {
+              ptx::mbar_arrive(&full[s]);
+            } else {
+              ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + sf_bytes * (1 + nsfb));
+              ptx::tma_load_2d(st, &tmap_a, kb * kBKBytes, m0, &full[s]);
+              ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, n0, &full[s]);
+              ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)mt * kc_total + kb * 4) * 512, sf_bytes,
+                             &full[s]);
+              for (int j = 0; j < nsfb; ++j)
+                ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + j * 2048,
+                               p.sfb + ((size_t)(nt * Cfg::NB + j) * kc_total + kb * 4) * 512, sf_bytes, &full[s]);
+            }
+          }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = ptx::make_idesc_nvfp4(kBM, BN);
       uint32_t it = 0, tile_it = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
@@ -153,6 +162,7 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const uint32_t sfa_t = tmem_base + Cfg::SF_COL0 + (it & 1) * Cfg::SF_COLS, sfb_t = sfa_t + 16;
           const uint64_t a_desc = ptx::make_sw128_kmajor_desc(a_addr);
           const uint64_t b_desc = ptx::make_sw128_kmajor_desc(b_addr);
+          if (ptx::elect_one()) {
           for (int c = 0; c < kchunks; ++c) {
             if (!(p.debug & 4)) {
               ptx::tc_cp_32x128b_warpx4(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
@@ -166,8 +176,11 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                                 sfa_t + c * 4, sfb_t + c * 4 * Cfg::NB);
           }
           ptx::tc_commit(&empty[s]);  // frees the smem stage once these MMAs have read it
+          }
+          __syncwarp();
         }
-        ptx::tc_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        if (ptx::elect_one()) ptx::tc_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        __syncwarp();
       }
     }
   } else {

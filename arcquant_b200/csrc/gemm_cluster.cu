@@ -104,8 +104,8 @@ gemm_nvfp4_cluster_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
   constexpr uint16_t all_mask = (uint16_t)((1u << Cfg::CSZ) - 1);
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp loops; elect.sync leader issues) =====================
+    {
       uint32_t it = 0;
       for (int st = cluster_id; st < num_stiles; st += num_clusters) {
         const int mt = (st % p.stiles_m) * CM + cm, nt = (st / p.stiles_m) * CN + cn;
@@ -119,6 +119,7 @@ gemm_nvfp4_cluster_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           uint8_t *stg = smem + s * Cfg::STAGE_BYTES;
           int kchunks = kc_total - kb * 4;
           if (kchunks > 4) kchunks = 4;
+          if (ptx::elect_one()) {
           ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + (a_ok ? kchunks * 512 : 0) + nsfb * kchunks * 512);
           // my slice of the A tile -> all row peers; my slice of the B tile -> all column peers
           ptx::tma_load_2d_mc(stg + cn * Cfg::A_SLICE_ROWS * kBKBytes, &tmap_a, kb * kBKBytes,
@@ -149,12 +150,14 @@ gemm_nvfp4_cluster_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
               q0 += cnt;
             }
           }
+          }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = ptx::make_idesc_nvfp4(kBM, kBN);
       uint32_t it = 0, tile_it = 0;
       for (int st = cluster_id; st < num_stiles; st += num_clusters, ++tile_it) {
@@ -169,6 +172,7 @@ gemm_nvfp4_cluster_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
           if (kchunks > 4) kchunks = 4;
           const uint32_t a_addr = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES), b_addr = a_addr + Cfg::A_BYTES;
           const uint32_t sfa_addr = b_addr + Cfg::B_BYTES, sfb_addr = sfa_addr + Cfg::SFA_BYTES;
+          if (ptx::elect_one()) {
           for (int c = 0; c < kchunks; ++c) {
             ptx::tc_cp_32x128b_warpx4(tmem_base + Cfg::SFA_COL + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
             ptx::tc_cp_32x128b_warpx4(tmem_base + Cfg::SFB_COL + c * 8, ptx::make_sf_desc(sfb_addr + c * 512));
@@ -179,8 +183,11 @@ gemm_nvfp4_cluster_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gr
             ptx::tc_mma_nvfp4(tmem_base, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
                               tmem_base + Cfg::SFA_COL + c * 4, tmem_base + Cfg::SFB_COL + c * 8);
           ptx::tc_commit_mc(&empty[s], all_mask);  // stage s consumed here -> tell every producer in the cluster
+          }
+          __syncwarp();
         }
-        ptx::tc_commit(tfull);
+        if (ptx::elect_one()) ptx::tc_commit(tfull);
+        __syncwarp();
       }
     }
   } else {
