@@ -33,7 +33,7 @@ constexpr int kBK = 256;
 constexpr int kGemmThreads = 320;
 constexpr int kEpiWarps = 8;
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int PC = 64>
 struct GemmCfg {
   static constexpr int NB = BN / 128;                 // 128-row scale blocks per B tile
   static constexpr int A_BYTES = kBM * kBKBytes;      // 16 KiB
@@ -45,7 +45,8 @@ struct GemmCfg {
   static constexpr int SF_COLS = 16 + 16 * NB;        // one scale-factor buffer: SFA (16 cols) then SFB
   static constexpr int SF_COL0 = ACC_STAGES * BN;     // TMEM columns: accumulators, then 2 scale-factor buffers
   static constexpr int TMEM_COLS = 512;
-  static constexpr int EPI_BYTES = kEpiWarps * 4096;  // per-warp 32 rows x 128 B staging
+  static constexpr int EPI_WARP_BYTES = 32 * PC * 2;   // per-warp staging: 32 rows x PC bf16 columns per pass
+  static constexpr int EPI_BYTES = kEpiWarps * EPI_WARP_BYTES;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
   static_assert(SF_COL0 + 2 * SF_COLS <= TMEM_COLS, "TMEM overflow");
   static_assert(SMEM_BYTES <= 232448, "shared memory overflow");
@@ -62,11 +63,11 @@ struct GemmParams {
   int debug;  // experiments only: bit0 = skip TMA loads, bit1 = skip MMA issue, bit2 = skip UTCCP, bit3 = skip stores
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int PC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const GemmParams p) {
-  using Cfg = GemmCfg<BN, STAGES>;
+  using Cfg = GemmCfg<BN, STAGES, PC>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t *epi = smem + STAGES * Cfg::STAGE_BYTES;
@@ -106,6 +107,7 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // UTCCP, UTCOMMA, UTCBAR -- in an ELECT/R2UR.BROADCAST waterfall loop: ~45 ns per instruction measured.)
     {
       uint32_t it = 0;
+      uint32_t ready = ptx::mbar_test(&empty[0], 1);
       const int nblk_total = (p.N + 127) / 128;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
@@ -115,7 +117,8 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
-          ptx::mbar_wait(&empty[s], ph ^ 1);
+          if (!ready) ptx::mbar_wait(&empty[s], ph ^ 1);
+          ready = ptx::mbar_test(&empty[(it + 1) % STAGES], (((it + 1) / STAGES) & 1) ^ 1);  // peek: consumed next iteration
           uint8_t *st = smem + s * Cfg::STAGE_BYTES;
           int kchunks = kc_total - kb * 4;
           if (kchunks > 4) kchunks = 4;
@@ -143,6 +146,7 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     {
       constexpr uint32_t idesc = ptx::make_idesc_nvfp4(kBM, BN);
       uint32_t it = 0, tile_it = 0;
+      uint32_t ready = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
         const int acc = tile_it % Cfg::ACC_STAGES;
         const uint32_t acc_ph = (tile_it / Cfg::ACC_STAGES) & 1;
@@ -152,7 +156,8 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
-          ptx::mbar_wait(&full[s], ph);
+          if (!ready) ptx::mbar_wait(&full[s], ph);
+          ready = ptx::mbar_test(&full[(it + 1) % STAGES], ((it + 1) / STAGES) & 1);  // peek: consumed next iteration
           ptx::tc_fence_after();
           uint8_t *st = smem + s * Cfg::STAGE_BYTES;
           int kchunks = kc_total - kb * 4;
@@ -175,11 +180,12 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               ptx::tc_mma_nvfp4(d_tmem, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
                                 sfa_t + c * 4, sfb_t + c * 4 * Cfg::NB);
           }
+          if (p.debug & 16) ptx::mbar_arrive(&empty[s]); else
           ptx::tc_commit(&empty[s]);  // frees the smem stage once these MMAs have read it
           }
           __syncwarp();
         }
-        if (ptx::elect_one()) ptx::tc_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        if (ptx::elect_one()) { if (p.debug & 16) ptx::mbar_arrive(&tfull[acc]); else ptx::tc_commit(&tfull[acc]); }  // accumulator complete -> epilogue
         __syncwarp();
       }
     }
@@ -189,7 +195,9 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int q = warp & 3, half = (warp - 2) >> 2;
     float alpha = p.alpha;
     if (p.alpha_dev) alpha = __ldg(p.alpha_dev);
-    uint8_t *wst = epi + (warp - 2) * 4096;
+    uint8_t *wst = epi + (warp - 2) * Cfg::EPI_WARP_BYTES;
+    constexpr int CH = PC / 8;        // 16-byte chunks per staged row
+    constexpr int RB = PC * 2;        // staged row bytes
     const bool vec_ok = (p.N % 8) == 0;
     uint32_t tile_it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
@@ -200,35 +208,37 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + half * HC;
       uint32_t r[HC / 32][32];
+      if (!(p.debug & 32)) {
 #pragma unroll
       for (int cb = 0; cb < HC / 32; ++cb) ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r[cb]);
       ptx::tmem_ld_wait();
+      }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty[acc]);  // accumulator is in registers: the next MMAs may start
       if (p.debug & 8) continue;
 #pragma unroll
-      for (int pass = 0; pass < HC / 64; ++pass) {
-        // lane = row: 64 columns -> 8 chunks of 8 bf16, chunk j at swizzled slot j ^ (row & 7)
+      for (int pass = 0; pass < HC / PC; ++pass) {
+        // lane = row: PC columns -> CH chunks of 8 bf16, chunk j at swizzled slot j ^ (row & (CH-1))
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < CH; ++j) {
           uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const int col = pass * 64 + j * 8 + 2 * e;
+            const int col = pass * PC + j * 8 + 2 * e;
             __nv_bfloat162 h2 = __floats2bfloat162_rn(alpha * __uint_as_float(r[col >> 5][col & 31]),
                                                       alpha * __uint_as_float(r[col >> 5][(col & 31) + 1]));
             o[e] = *reinterpret_cast<uint32_t *>(&h2);
           }
-          *reinterpret_cast<uint4 *>(wst + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<uint4 *>(wst + lane * RB + ((j ^ (lane & (CH - 1))) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
         __syncwarp();
-        const int j = lane & 7;
-        const int gcol = nt * BN + half * HC + pass * 64 + j * 8;
+        const int j = lane & (CH - 1);
+        const int gcol = nt * BN + half * HC + pass * PC + j * 8;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = i * 4 + (lane >> 3);
-          const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * 128 + ((j ^ (rr & 7)) << 4));
+        for (int i = 0; i < CH; ++i) {  // 32 / CH rows per instruction, CH instructions
+          const int rr = i * (32 / CH) + lane / CH;
+          const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
           const int grow = mt * kBM + q * 32 + rr;
           if (grow < p.M && gcol < p.N) {
             __nv_bfloat16 *dst = p.d + (size_t)grow * p.N + gcol;
@@ -312,10 +322,10 @@ int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t 
   return ARCQ_OK;
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int PC>
 static int launch_gemm(const void *a, const void *b, GemmParams p, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, STAGES>;
-  auto kern = gemm_nvfp4_kernel<BN, STAGES>;
+  using Cfg = GemmCfg<BN, STAGES, PC>;
+  auto kern = gemm_nvfp4_kernel<BN, STAGES, PC>;
   static bool attr_set = false;
   if (!attr_set) {
     ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -373,6 +383,8 @@ extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, co
     // wide tiles halve A re-reads and MMA issue count; narrow tiles fill the SMs for small problems
     bn = (tiles256 >= 2 * (int64_t)sm_count() || N % 256 == 0) && N > 128 ? 256 : 128;
   }
-  if (bn == 256) return launch_gemm<256, 3>(a, b, p, st);
-  return launch_gemm<128, 5>(a, b, p, st);
+  const char *es = getenv("ARCQ_GEMM_STAGES");
+  const int stages = es ? atoi(es) : 4;
+  if (bn == 256) return stages == 3 ? launch_gemm<256, 3, 64>(a, b, p, st) : launch_gemm<256, 4, 16>(a, b, p, st);
+  return launch_gemm<128, 5, 64>(a, b, p, st);
 }

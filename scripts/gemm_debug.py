@@ -10,7 +10,7 @@ for (M, N, K) in [(8192, 14336, 4352), (8192, 4096, 14848)]:
     y = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
     for bn in ("256",):
         os.environ["ARCQ_GEMM_BN"] = bn
-        for dbg, name in [(0, "full"), (1, "no-loads"), (2, "no-mma(+utccp on)"), (6, "no-mma no-utccp"), (4, "mma, no-utccp"), (5, "no-loads no-utccp"), (7, "nothing"), (8, "full, no stores"), (15, "nothing, no stores")]:
+        for dbg, name in [(0, "full"), (1, "no-loads"), (6, "no-mma no-utccp"), (5, "no-loads no-utccp"), (7, "nothing"), (8, "full, no stores")]:
             os.environ["ARCQ_GEMM_DEBUG"] = str(dbg)
             for _ in range(3):
                 agemm.matmul(a, b, sfa, sfb, 1e-3, out=y)
