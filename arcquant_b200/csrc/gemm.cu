@@ -322,6 +322,30 @@ int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t 
   return ARCQ_OK;
 }
 
+// scale-factor buffer as a 2-D map of 512-byte atoms (row = one 128-row x 64-k atom): box = 4 atoms = the
+// 2 KB a k-block needs; out-of-range atoms (K tail, row-block tail) read as zeros
+int cached_sf_map(CUtensorMap *out, const void *ptr, int64_t natoms) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  MapKey key{ptr, natoms, 512, -4};
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return ARCQ_OK; }
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return ARCQ_ECUDA; }
+  cuuint64_t dims[2] = {128, (cuuint64_t)natoms};
+  cuuint64_t strides[1] = {512};
+  cuuint32_t box[2] = {128, 4};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (scale factors) failed with CUresult %d", (int)r); return ARCQ_ECUDA; }
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, *out);
+  return ARCQ_OK;
+}
+
 template <int BN, int STAGES, int PC>
 static int launch_gemm(const void *a, const void *b, GemmParams p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, STAGES, PC>;
@@ -353,7 +377,10 @@ using namespace arcq;
 namespace arcq {
 int launch_gemm_cluster(int shape, const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K,
                         float alpha, const float *alpha_dev, void *d, cudaStream_t stream);
+int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
+                     const float *alpha_dev, void *d, cudaStream_t stream);
 }
+static const int kDefaultPair = 0;  // set once the cta_group::2 kernel is validated on hardware
 static const int kDefaultClusterShape = 0;  // set once the cluster kernel is validated on hardware
 
 extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
@@ -371,6 +398,10 @@ extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, co
   cudaStream_t st = (cudaStream_t)stream;
   // ARCQ_GEMM_CLUSTER=<10*CM+CN> forces a multicast cluster shape (0 = never), ARCQ_GEMM_BN forces the tile
   // width of the non-cluster kernel; both are for experiments, the defaults below are the tuned choice.
+  const char *ep = getenv("ARCQ_GEMM_PAIR");
+  const int64_t ptiles = ((M + 255) / 256) * ((N + 255) / 256);
+  const int use_pair = ep ? atoi(ep) : (kDefaultPair && ptiles >= sm_count() / 2);
+  if (use_pair) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, d, st);
   const char *ec = getenv("ARCQ_GEMM_CLUSTER");
   int cshape = ec ? atoi(ec) : -1;
   const int64_t tiles256 = ((M + kBM - 1) / kBM) * ((N + 255) / 256);

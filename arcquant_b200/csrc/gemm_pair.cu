@@ -1,0 +1,268 @@
+// gemm_pair.cu -- NVFP4 block-scaled GEMM with tcgen05 `cta_group::2`: two CTAs on the two SMs of a TPC
+// compute one 256 x 256 output tile; each keeps its own 128 rows of A, HALF of the B tile (128 of the 256
+// n-rows) and its own 128 x 256 fp32 accumulator in TMEM.  The tensor cores read the peer's half of B across
+// the SM pair, so an SM ingests 16 KB (A) + 16 KB (B/2) + 6 KB (scale factors) per 256-deep k-block instead of
+// the 54 KB of the single-CTA kernel (gemm.cu) -- measured there: the 64 B/clk/SM L2->SM ingest, not the
+// tensor pipe, is what bounds a 128 x 256 single-CTA tile (profiles/r1_gemm_notes.md).
+//
+// Protocol (cluster = the CTA pair; rank 0 = leader):
+//   full[s]   (leader's copy is the live one) count 1: the leader's producer posts expect_tx for BOTH CTAs'
+//             bytes; every TMA of either CTA is issued with .cta_group::2 and credits the LEADER's barrier.
+//   empty[s]  one per CTA, count 1: the leader's MMA thread commits with a multicast to both CTAs.
+//   tfull     one per CTA, count 1: multicast commit after the last k-block.
+//   tempty    leader's copy, count 16: all eight epilogue warps of both CTAs arrive (remote arrive from rank 1).
+// Only the leader issues tcgen05.cp / tcgen05.mma (cta_group::2 makes both SMs execute them on their own
+// shared memory / TMEM at the same offsets).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace arcq {
+
+int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t row_bytes, int box_rows);
+int cached_sf_map(CUtensorMap *out, const void *ptr, int64_t natoms);
+
+namespace {
+
+constexpr int kRows = 128;                 // rows of A (and of the B half) per CTA
+constexpr int kBN = 256, kBKBytes = 128, kBK = 256;
+constexpr int kThreadsP = 320;             // warp 0 TMA, warp 1 MMA (leader only issues), warps 2..9 epilogue
+constexpr int kPC = 64;                    // epilogue staging pass width (columns)
+
+template <int STAGES>
+struct PCfg {
+  static constexpr int A_BYTES = kRows * kBKBytes;     // 16 KiB
+  static constexpr int B_BYTES = kRows * kBKBytes;     // this CTA's half of the B tile
+  static constexpr int SFA_BYTES = 4 * 512;
+  static constexpr int SFB_BYTES = 2 * 4 * 512;        // both 128-row scale blocks of the 256-wide tile
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + SFA_BYTES + SFB_BYTES;   // 38912
+  static constexpr int SF_COLS = 48, SF_COL0 = kBN, TMEM_COLS = 512;
+  static constexpr int EPI_WARP_BYTES = 32 * kPC * 2;
+  static constexpr int EPI_BYTES = 8 * EPI_WARP_BYTES;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+  static_assert(SMEM_BYTES <= 232448, "shared memory overflow");
+};
+
+struct PParams {
+  __nv_bfloat16 *d;
+  const float *alpha_dev;
+  float alpha;
+  int M, N, K;
+  int ptiles_m, ptiles_n;   // 256 x 256 pair tiles
+};
+
+template <int STAGES>
+__global__ void __launch_bounds__(kThreadsP, 1)
+gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                       const __grid_constant__ CUtensorMap tmap_sfa, const __grid_constant__ CUtensorMap tmap_sfb,
+                       const PParams p) {
+  using Cfg = PCfg<STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t *epi = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(epi + Cfg::EPI_BYTES);
+  uint64_t *full = bars, *empty = bars + STAGES, *tfull = bars + 2 * STAGES, *tempty = tfull + 1;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();     // 0 = leader
+  const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int K = p.K, nkb = (K + kBK - 1) / kBK, kc_total = K / 64;
+  const int num_ptiles = p.ptiles_m * p.ptiles_n;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    ptx::prefetch_tmap(&tmap_sfa);
+    ptx::prefetch_tmap(&tmap_sfb);
+    for (int s = 0; s < STAGES; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], 1); }
+    ptx::mbar_init(tfull, 1);
+    ptx::mbar_init(tempty, 16);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS);
+    ptx::tmem_relinquish_pair();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs; completion bytes go to the leader's full[s]) ==========
+    uint32_t it = 0;
+    uint32_t ready = ptx::mbar_test(&empty[0], 1);
+    for (int t = pair_id; t < num_ptiles; t += num_pairs) {
+      const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
+      const int mblk = pm * 2 + (int)rank;        // this CTA's 128-row block of A / SFA
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        if (!ready) ptx::mbar_wait(&empty[s], ph ^ 1);
+        ready = ptx::mbar_test(&empty[(it + 1) % STAGES], (((it + 1) / STAGES) & 1) ^ 1);
+        uint8_t *st = smem + s * Cfg::STAGE_BYTES;
+        if (ptx::elect_one()) {
+          const uint32_t lbar = ptx::mapa(&full[s], 0);
+          if (rank == 0) ptx::mbar_arrive_expect_tx(&full[s], 2 * Cfg::STAGE_BYTES);
+          ptx::tma_load_2d_pair(st, &tmap_a, kb * kBKBytes, mblk * kRows, lbar);
+          ptx::tma_load_2d_pair(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, pn * kBN + (int)rank * kRows, lbar);
+          // scale factors: rows of the SF maps are 512-B atoms, atom index = block * (K/64) + chunk
+          ptx::tma_load_2d_pair(st + Cfg::A_BYTES + Cfg::B_BYTES, &tmap_sfa, 0, mblk * kc_total + kb * 4, lbar);
+          ptx::tma_load_2d_pair(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES, &tmap_sfb, 0,
+                                (pn * 2) * kc_total + kb * 4, lbar);
+          ptx::tma_load_2d_pair(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + 2048, &tmap_sfb, 0,
+                                (pn * 2 + 1) * kc_total + kb * 4, lbar);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (rank == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_nvfp4(256, kBN);
+      uint32_t it = 0, tile_it = 0, ready = 0;
+      for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
+        ptx::mbar_wait(tempty, (tile_it & 1) ^ 1);
+        ptx::tc_fence_after();
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1;
+          if (!ready) ptx::mbar_wait(&full[s], ph);
+          ready = ptx::mbar_test(&full[(it + 1) % STAGES], ((it + 1) / STAGES) & 1);
+          ptx::tc_fence_after();
+          int kchunks = kc_total - kb * 4;
+          if (kchunks > 4) kchunks = 4;
+          const uint32_t a_addr = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES), b_addr = a_addr + Cfg::A_BYTES;
+          const uint32_t sfa_addr = b_addr + Cfg::B_BYTES, sfb_addr = sfa_addr + Cfg::SFA_BYTES;
+          const uint32_t sfa_t = tmem_base + Cfg::SF_COL0 + (it & 1) * Cfg::SF_COLS, sfb_t = sfa_t + 16;
+          const uint64_t a_desc = ptx::make_sw128_kmajor_desc(a_addr), b_desc = ptx::make_sw128_kmajor_desc(b_addr);
+          if (ptx::elect_one()) {
+            for (int c = 0; c < kchunks; ++c) {
+              ptx::tc_cp_32x128b_warpx4_pair(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
+              ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8, ptx::make_sf_desc(sfb_addr + c * 512));
+              ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8 + 4, ptx::make_sf_desc(sfb_addr + 2048 + c * 512));
+              ptx::tc_mma_nvfp4_pair(tmem_base, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
+                                     sfa_t + c * 4, sfb_t + c * 8);
+            }
+            ptx::tc_commit_pair(&empty[s], 3);   // both CTAs' stage s may be refilled
+          }
+          __syncwarp();
+        }
+        if (ptx::elect_one()) ptx::tc_commit_pair(tfull, 3);
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9 of both CTAs) =====================
+    constexpr int HC = kBN / 2, CH = kPC / 8, RB = kPC * 2;
+    const int q = warp & 3, half = (warp - 2) >> 2;
+    float alpha = p.alpha;
+    if (p.alpha_dev) alpha = __ldg(p.alpha_dev);
+    uint8_t *wst = epi + (warp - 2) * Cfg::EPI_WARP_BYTES;
+    const bool vec_ok = (p.N % 8) == 0;
+    const uint32_t tempty_leader = ptx::mapa(tempty, 0);
+    uint32_t tile_it = 0;
+    for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
+      const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
+      ptx::mbar_wait(tfull, tile_it & 1);
+      ptx::tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + half * HC;
+      uint32_t r[HC / 32][32];
+#pragma unroll
+      for (int cb = 0; cb < HC / 32; ++cb) ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r[cb]);
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader);
+      const int row_base = (pm * 2 + (int)rank) * kRows + q * 32;
+#pragma unroll
+      for (int pass = 0; pass < HC / kPC; ++pass) {
+#pragma unroll
+        for (int j = 0; j < CH; ++j) {
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int col = pass * kPC + j * 8 + 2 * e;
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(alpha * __uint_as_float(r[col >> 5][col & 31]),
+                                                      alpha * __uint_as_float(r[col >> 5][(col & 31) + 1]));
+            o[e] = *reinterpret_cast<uint32_t *>(&h2);
+          }
+          *reinterpret_cast<uint4 *>(wst + lane * RB + ((j ^ (lane & (CH - 1))) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+        __syncwarp();
+        const int j = lane & (CH - 1);
+        const int gcol = pn * kBN + half * HC + pass * kPC + j * 8;
+#pragma unroll
+        for (int i = 0; i < CH; ++i) {
+          const int rr = i * (32 / CH) + lane / CH;
+          const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
+          const int grow = row_base + rr;
+          if (grow < p.M && gcol < p.N) {
+            __nv_bfloat16 *dst = p.d + (size_t)grow * p.N + gcol;
+            if (vec_ok && gcol + 8 <= p.N) {
+              *reinterpret_cast<uint4 *>(dst) = v;
+            } else {
+              const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+              for (int e = 0; e < 8; ++e)
+                if (gcol + e < p.N) dst[e] = __ushort_as_bfloat16((unsigned short)(w[e >> 1] >> (16 * (e & 1))));
+            }
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync();
+  if (warp == 1) ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+}
+
+}  // namespace
+
+int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
+                     const float *alpha_dev, void *d, cudaStream_t stream) {
+  constexpr int STAGES = 5;
+  using Cfg = PCfg<STAGES>;
+  auto kern = gemm_nvfp4_pair_kernel<STAGES>;
+  static int max_pairs = -1;
+  cudaLaunchConfig_t cfg = {};
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.blockDim = dim3(kThreadsP);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = stream;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  if (max_pairs < 0) {
+    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    cfg.gridDim = dim3(2 * 74);
+    int n = 0;
+    ARCQ_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
+    max_pairs = n;
+  }
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, alpha, M, N, K, (M + 255) / 256, (N + 255) / 256};
+  const int64_t kc = K / 64;
+  CUtensorMap ta, tb, tsa, tsb;
+  if (int rc = cached_operand_map(&ta, a, M, K / 2, kRows)) return rc;
+  if (int rc = cached_operand_map(&tb, b, N, K / 2, kRows)) return rc;
+  if (int rc = cached_sf_map(&tsa, sfa, (int64_t)((M + 127) / 128) * kc)) return rc;
+  if (int rc = cached_sf_map(&tsb, sfb, (int64_t)((N + 127) / 128) * kc)) return rc;
+  int pairs = p.ptiles_m * p.ptiles_n;
+  if (pairs > max_pairs) pairs = max_pairs;
+  cfg.gridDim = dim3(2 * pairs);
+  ARCQ_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, ta, tb, tsa, tsb, p));
+  count_launch();
+  return ARCQ_OK;
+}
+
+}  // namespace arcq

@@ -34,11 +34,13 @@ def main():
         M, N, K = [int(v) for v in sh.split(",")]
         a, b, sfa, sfb = rand_operands(M, N, K, dev)
         os.environ["ARCQ_GEMM_CLUSTER"] = "0"
+        os.environ["ARCQ_GEMM_PAIR"] = "0"
         os.environ["ARCQ_GEMM_BN"] = "256"
         base = agemm.matmul(a, b, sfa, sfb, 1e-3)
         torch.cuda.synchronize()
         for cs in args.clusters.split(","):
-            os.environ["ARCQ_GEMM_CLUSTER"] = cs
+            os.environ["ARCQ_GEMM_PAIR"] = "1" if cs == "p" else "0"
+            os.environ["ARCQ_GEMM_CLUSTER"] = "0" if cs == "p" else cs
             y = torch.empty_like(base)
             for _ in range(3):
                 agemm.matmul(a, b, sfa, sfb, 1e-3, out=y)
