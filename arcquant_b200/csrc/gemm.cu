@@ -380,7 +380,7 @@ int launch_gemm_cluster(int shape, const void *a, const void *b, const void *sfa
 int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
                      const float *alpha_dev, void *d, cudaStream_t stream);
 }
-static const int kDefaultPair = 0;  // set once the cta_group::2 kernel is validated on hardware
+static const int kDefaultPair = 1;  // cta_group::2 kernel for shapes with at least one 256x256 tile per SM pair
 static const int kDefaultClusterShape = 0;  // set once the cluster kernel is validated on hardware
 
 extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,

@@ -18,6 +18,13 @@
 #include "common.cuh"
 #include "ptx.cuh"
 
+// per-role cycle counters (scripts/gemm_prof.py): build with -DARCQ_GEMM_PROFILE, run with ARCQ_GEMM_PROF=1
+#ifdef ARCQ_GEMM_PROFILE
+#define PROF(...) __VA_ARGS__
+#else
+#define PROF(...)
+#endif
+
 namespace arcq {
 
 int cached_operand_map(CUtensorMap *out, const void *ptr, int64_t rows, int64_t row_bytes, int box_rows);
@@ -50,6 +57,8 @@ struct PParams {
   float alpha;
   int M, N, K;
   int ptiles_m, ptiles_n;   // 256 x 256 pair tiles
+  int debug;                // experiments: bit0 skip loads, bit1 skip MMA, bit2 skip UTCCP, bit3 skip stores
+  long long *prof;          // experiments: per-role cycle counters of block 0/1 (nullable)
 };
 
 template <int STAGES>
@@ -94,6 +103,7 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   if (warp == 0) {
     // ===================== TMA producer (both CTAs; completion bytes go to the leader's full[s]) ==========
     uint32_t it = 0;
+    PROF(long long pw = 0, pw_n = 0, pt0 = clock64();)
     uint32_t ready = ptx::mbar_test(&empty[0], 1);
     for (int t = pair_id; t < num_ptiles; t += num_pairs) {
       const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
@@ -101,11 +111,14 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
-        if (!ready) ptx::mbar_wait(&empty[s], ph ^ 1);
+        PROF(long long tp0 = clock64();)
+        if (!ready) { ptx::mbar_wait(&empty[s], ph ^ 1); PROF(++pw_n;) }
+        PROF(pw += clock64() - tp0;)
         ready = ptx::mbar_test(&empty[(it + 1) % STAGES], (((it + 1) / STAGES) & 1) ^ 1);
         uint8_t *st = smem + s * Cfg::STAGE_BYTES;
         if (ptx::elect_one()) {
           const uint32_t lbar = ptx::mapa(&full[s], 0);
+          if (p.debug & 1) { if (rank == 0) ptx::mbar_arrive(&full[s]); } else {
           if (rank == 0) ptx::mbar_arrive_expect_tx(&full[s], 2 * Cfg::STAGE_BYTES);
           ptx::tma_load_2d_pair(st, &tmap_a, kb * kBKBytes, mblk * kRows, lbar);
           ptx::tma_load_2d_pair(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, pn * kBN + (int)rank * kRows, lbar);
@@ -115,22 +128,29 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
                                 (pn * 2) * kc_total + kb * 4, lbar);
           ptx::tma_load_2d_pair(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + 2048, &tmap_sfb, 0,
                                 (pn * 2 + 1) * kc_total + kb * 4, lbar);
+          }
         }
         __syncwarp();
       }
     }
+    PROF(if (p.prof && blockIdx.x < 2 && lane == 0) { long long *o = p.prof + blockIdx.x * 16; o[0] = clock64() - pt0; o[1] = pw; o[2] = pw_n; o[3] = it; })
   } else if (warp == 1) {
     // ===================== MMA issuer (leader CTA only) =====================
     if (rank == 0) {
       constexpr uint32_t idesc = ptx::make_idesc_nvfp4(256, kBN);
       uint32_t it = 0, tile_it = 0, ready = 0;
+      PROF(long long cw = 0, cw_n = 0, ce = 0, ct0 = clock64();)
       for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
+        PROF(long long t0e = clock64();)
         ptx::mbar_wait(tempty, (tile_it & 1) ^ 1);
+        PROF(ce += clock64() - t0e;)
         ptx::tc_fence_after();
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1;
-          if (!ready) ptx::mbar_wait(&full[s], ph);
+          PROF(long long t0f = clock64();)
+          if (!ready) { ptx::mbar_wait(&full[s], ph); PROF(++cw_n;) }
+          PROF(cw += clock64() - t0f;)
           ready = ptx::mbar_test(&full[(it + 1) % STAGES], ((it + 1) / STAGES) & 1);
           ptx::tc_fence_after();
           int kchunks = kc_total - kb * 4;
@@ -141,9 +161,12 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           const uint64_t a_desc = ptx::make_sw128_kmajor_desc(a_addr), b_desc = ptx::make_sw128_kmajor_desc(b_addr);
           if (ptx::elect_one()) {
             for (int c = 0; c < kchunks; ++c) {
+              if (!(p.debug & 4)) {
               ptx::tc_cp_32x128b_warpx4_pair(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
               ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8, ptx::make_sf_desc(sfb_addr + c * 512));
               ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8 + 4, ptx::make_sf_desc(sfb_addr + 2048 + c * 512));
+              }
+              if (!(p.debug & 2))
               ptx::tc_mma_nvfp4_pair(tmem_base, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
                                      sfa_t + c * 4, sfb_t + c * 8);
             }
@@ -154,6 +177,7 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         if (ptx::elect_one()) ptx::tc_commit_pair(tfull, 3);
         __syncwarp();
       }
+      PROF(if (p.prof && blockIdx.x == 0 && lane == 0) { long long *o = p.prof + 4; o[0] = clock64() - ct0; o[1] = cw; o[2] = cw_n; o[3] = ce; o[4] = it; o[5] = tile_it; })
     }
   } else {
     // ===================== epilogue (warps 2..9 of both CTAs) =====================
@@ -165,9 +189,12 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     const bool vec_ok = (p.N % 8) == 0;
     const uint32_t tempty_leader = ptx::mapa(tempty, 0);
     uint32_t tile_it = 0;
+    PROF(long long ew = 0, eld = 0, et0 = clock64();)
     for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
       const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
+      PROF(long long e0 = clock64();)
       ptx::mbar_wait(tfull, tile_it & 1);
+      PROF(long long e1 = clock64(); ew += e1 - e0;)
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + half * HC;
       uint32_t r[HC / 32][32];
@@ -177,6 +204,8 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader);
+      PROF(eld += clock64() - e1;)
+      if (p.debug & 8) continue;
       const int row_base = (pm * 2 + (int)rank) * kRows + q * 32;
 #pragma unroll
       for (int pass = 0; pass < HC / kPC; ++pass) {
@@ -215,6 +244,7 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         __syncwarp();
       }
     }
+    PROF(if (p.prof && blockIdx.x == 0 && warp == 2 && lane == 0) { long long *o = p.prof + 10; o[0] = clock64() - et0; o[1] = ew; o[2] = eld; })
   }
 
   ptx::tc_fence_before();
@@ -250,7 +280,11 @@ int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *
     if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
     max_pairs = n;
   }
-  PParams p{(__nv_bfloat16 *)d, alpha_dev, alpha, M, N, K, (M + 255) / 256, (N + 255) / 256};
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, alpha, M, N, K, (M + 255) / 256, (N + 255) / 256, 0, nullptr};
+  static long long *prof_buf = nullptr;
+  const bool do_prof = getenv("ARCQ_GEMM_PROF") != nullptr;
+  if (do_prof) { if (!prof_buf) cudaMalloc(&prof_buf, 64 * 8); cudaMemsetAsync(prof_buf, 0, 64 * 8, stream); p.prof = prof_buf; }
+  if (const char *dbg = getenv("ARCQ_GEMM_DEBUG")) p.debug = atoi(dbg);
   const int64_t kc = K / 64;
   CUtensorMap ta, tb, tsa, tsb;
   if (int rc = cached_operand_map(&ta, a, M, K / 2, kRows)) return rc;
@@ -262,6 +296,16 @@ int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *
   cfg.gridDim = dim3(2 * pairs);
   ARCQ_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, ta, tb, tsa, tsb, p));
   count_launch();
+  if (do_prof) {
+    long long h[64];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h, prof_buf, sizeof(h), cudaMemcpyDeviceToHost);
+    fprintf(stderr, "[prof] producer0: total %lld clk, wait-empty %lld clk in %lld blocking waits of %lld iters | producer1: total %lld wait %lld (%lld)\n",
+            h[0], h[1], h[2], h[3], h[16], h[17], h[18]);
+    fprintf(stderr, "[prof] mma: total %lld clk, wait-full %lld clk in %lld blocking waits of %lld iters, wait-tempty %lld clk over %lld tiles\n",
+            h[4], h[5], h[6], h[8], h[7], h[9]);
+    fprintf(stderr, "[prof] epilogue warp2: total %lld clk, wait-tfull %lld clk, tmem-ld+release %lld clk\n", h[10], h[11], h[12]);
+  }
   return ARCQ_OK;
 }
 

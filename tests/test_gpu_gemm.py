@@ -61,6 +61,18 @@ def test_gemm_vs_dequant_matmul(M, N, KQ, KE):
     _run_case(M, N, KQ, KE, seed=M + N)
 
 
+@pytest.mark.parametrize("variant", ["pair", "bn128", "bn256", "cluster22"])
+@pytest.mark.parametrize("M,N,KQ,KE", [(256, 256, 256, 0), (300, 520, 1024, 64), (77, 1000, 2048, 128), (1024, 768, 4096, 256)])
+def test_gemm_kernel_variants(monkeypatch, variant, M, N, KQ, KE):
+    """Every kernel family (cta_group::2 pair, single-CTA 128/256-wide, multicast cluster) on ragged shapes."""
+    env = {"pair": {"ARCQ_GEMM_PAIR": "1"}, "bn128": {"ARCQ_GEMM_PAIR": "0", "ARCQ_GEMM_CLUSTER": "0", "ARCQ_GEMM_BN": "128"},
+           "bn256": {"ARCQ_GEMM_PAIR": "0", "ARCQ_GEMM_CLUSTER": "0", "ARCQ_GEMM_BN": "256"},
+           "cluster22": {"ARCQ_GEMM_PAIR": "0", "ARCQ_GEMM_CLUSTER": "22"}}[variant]
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    _run_case(M, N, KQ, KE, seed=M + N + 1)
+
+
 @pytest.mark.parametrize("bn", [128, 256])
 def test_gemm_device_alpha_and_identity(bn):
     """Known answer: codes 1.0 (0x2) everywhere, scales 1.0 (0x38): y = alpha * K."""
