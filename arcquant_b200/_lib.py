@@ -38,7 +38,7 @@ def load() -> ctypes.CDLL:
     global _L
     if _L is not None:
         return _L
-    path = _build.LIB
+    path = os.environ.get("ARCQ_LIB") or _build.LIB  # ARCQ_LIB: experiment builds (scripts/build_variant.py)
     if not os.path.exists(path) or (os.environ.get("ARCQ_REBUILD") == "1"):
         path = _build.build()
     try:

@@ -118,7 +118,7 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         uint8_t *st = smem + s * Cfg::STAGE_BYTES;
         if (ptx::elect_one()) {
           const uint32_t lbar = ptx::mapa(&full[s], 0);
-          if (p.debug & 1) { if (rank == 0) ptx::mbar_arrive(&full[s]); } else {
+          {
           if (rank == 0) ptx::mbar_arrive_expect_tx(&full[s], 2 * Cfg::STAGE_BYTES);
           ptx::tma_load_2d_pair(st, &tmap_a, kb * kBKBytes, mblk * kRows, lbar);
           ptx::tma_load_2d_pair(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, pn * kBN + (int)rank * kRows, lbar);
@@ -138,6 +138,11 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     // ===================== MMA issuer (leader CTA only) =====================
     if (rank == 0) {
       constexpr uint32_t idesc = ptx::make_idesc_nvfp4(256, kBN);
+      const uint32_t base = ptx::smem_u32(smem);
+      const uint64_t a_desc0 = ptx::make_sw128_kmajor_desc(base), b_desc0 = ptx::make_sw128_kmajor_desc(base + Cfg::A_BYTES);
+      const uint64_t sfa_desc0 = ptx::make_sf_desc(base + Cfg::A_BYTES + Cfg::B_BYTES);
+      const uint64_t sfb_desc0 = ptx::make_sf_desc(base + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES);
+      const uint32_t sf_t0 = tmem_base + Cfg::SF_COL0;
       uint32_t it = 0, tile_it = 0, ready = 0;
       PROF(long long cw = 0, cw_n = 0, ce = 0, ct0 = clock64();)
       for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
@@ -153,22 +158,28 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           PROF(cw += clock64() - t0f;)
           ready = ptx::mbar_test(&full[(it + 1) % STAGES], ((it + 1) / STAGES) & 1);
           ptx::tc_fence_after();
-          int kchunks = kc_total - kb * 4;
-          if (kchunks > 4) kchunks = 4;
-          const uint32_t a_addr = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES), b_addr = a_addr + Cfg::A_BYTES;
-          const uint32_t sfa_addr = b_addr + Cfg::B_BYTES, sfb_addr = sfa_addr + Cfg::SFA_BYTES;
-          const uint32_t sfa_t = tmem_base + Cfg::SF_COL0 + (it & 1) * Cfg::SF_COLS, sfb_t = sfa_t + 16;
-          const uint64_t a_desc = ptx::make_sw128_kmajor_desc(a_addr), b_desc = ptx::make_sw128_kmajor_desc(b_addr);
+          // descriptors of stage s: constant base + s * (stage bytes / 16) in the 14-bit address field
+          const uint32_t soff = (uint32_t)s * (Cfg::STAGE_BYTES >> 4);
+          const uint64_t a_desc = a_desc0 + soff, b_desc = b_desc0 + soff, sfa_desc = sfa_desc0 + soff, sfb_desc = sfb_desc0 + soff;
+          const uint32_t sfa_t = sf_t0 + (it & 1) * Cfg::SF_COLS, sfb_t = sfa_t + 16;
           if (ptx::elect_one()) {
-            for (int c = 0; c < kchunks; ++c) {
-              if (!(p.debug & 4)) {
-              ptx::tc_cp_32x128b_warpx4_pair(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
-              ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8, ptx::make_sf_desc(sfb_addr + c * 512));
-              ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8 + 4, ptx::make_sf_desc(sfb_addr + 2048 + c * 512));
+            if (kb + 1 < nkb || (kc_total & 3) == 0) {
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                ptx::tc_cp_32x128b_warpx4_pair(sfa_t + c * 4, sfa_desc + c * 32);
+                ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8, sfb_desc + c * 32);
+                ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8 + 4, sfb_desc + 128 + c * 32);
+                ptx::tc_mma_nvfp4_pair(tmem_base, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb | c) ? 1u : 0u, sfa_t + c * 4,
+                                       sfb_t + c * 8);
               }
-              if (!(p.debug & 2))
-              ptx::tc_mma_nvfp4_pair(tmem_base, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
-                                     sfa_t + c * 4, sfb_t + c * 8);
+            } else {  // K tail: the last k-block holds 1..3 chunks of 64
+              for (int c = 0; c < (kc_total & 3); ++c) {
+                ptx::tc_cp_32x128b_warpx4_pair(sfa_t + c * 4, sfa_desc + c * 32);
+                ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8, sfb_desc + c * 32);
+                ptx::tc_cp_32x128b_warpx4_pair(sfb_t + c * 8 + 4, sfb_desc + 128 + c * 32);
+                ptx::tc_mma_nvfp4_pair(tmem_base, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb | c) ? 1u : 0u, sfa_t + c * 4,
+                                       sfb_t + c * 8);
+              }
             }
             ptx::tc_commit_pair(&empty[s], 3);   // both CTAs' stage s may be refilled
           }
@@ -205,7 +216,6 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader);
       PROF(eld += clock64() - e1;)
-      if (p.debug & 8) continue;
       const int row_base = (pm * 2 + (int)rank) * kRows + q * 32;
 #pragma unroll
       for (int pass = 0; pass < HC / kPC; ++pass) {
