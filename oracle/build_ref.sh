@@ -11,7 +11,7 @@ OUT="$HERE/_ref"
 WHAT="${1:-all}"
 [ -d "$REF/kernels/src" ] || { echo "build_ref: $REF not present (GPU box?) -- using prebuilt $OUT"; exit 0; }
 mkdir -p "$OUT/tables"
-INC="-I$REF/kernels/include -I$REF/third-party/cutlass/include -I$REF/third-party/cutlass/tools/util/include"
+INC="-I$REF/kernels/include -I$REF/third-party/cutlass/include -I$REF/third-party/cutlass/tools/util/include -I$REF/third-party/cutlass/examples/common"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 if [ "$WHAT" = probe ] || [ "$WHAT" = all ]; then
   if [ ! -x "$OUT/ref_probe" ] || [ "$HERE/ref_probe.cu" -nt "$OUT/ref_probe" ]; then

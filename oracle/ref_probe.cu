@@ -120,12 +120,14 @@ int main(int argc, char **argv) {
   const int probs[3][2] = {{300, 4160}, {128, 64}, {257, 1088}};
   for (auto &pr : probs) {
     int rows = pr[0], K = pr[1];
-    auto layout = cute::filter_zeros(Cfg::tile_atom_to_shape_SFA(cute::make_shape(rows, 128, K, 1)));
+    // the unfiltered layout takes ELEMENT coordinates (the 16 elements of a group share one byte: stride 0);
+    // filter_zeros is only for the size of the buffer
+    auto layout = Cfg::tile_atom_to_shape_SFA(cute::make_shape(rows, 128, K, 1));
     std::vector<int32_t> off((size_t)rows * (K / 16));
     for (int r = 0; r < rows; ++r)
       for (int g = 0; g < K / 16; ++g) off[(size_t)r * (K / 16) + g] = (int32_t)layout(cute::make_coord(r, g * 16, 0));
     dump(dir + "/sf_offsets_" + std::to_string(rows) + "x" + std::to_string(K) + ".bin", off.data(), off.size() * 4);
-    int32_t cs = (int32_t)cute::cosize(layout);
+    int32_t cs = (int32_t)cute::cosize(cute::filter_zeros(layout));
     dump(dir + "/sf_cosize_" + std::to_string(rows) + "x" + std::to_string(K) + ".bin", &cs, 4);
   }
   printf("ref_probe: wrote tables to %s\n", dir.c_str());
