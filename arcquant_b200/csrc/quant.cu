@@ -13,50 +13,12 @@
 //  * the reorder index is read once per (group, tile) -- R-fold fewer index reads than one row per CTA;
 //  * e2m1 / e4m3 conversions use the sm_100a cvt instructions; scale bytes are assembled in shared
 //    memory and written as whole 4R-byte runs; codes leave as 8/16-byte coalesced stores.
-#include "common.cuh"
+#include "quant.cuh"
+#include <stdlib.h>
 
 namespace arcq {
 
 constexpr int kThreads = 256;
-constexpr float kFp4Max = 6.0f;          // reorder.cu:17
-constexpr float kFp8Max = 448.0f;        // reorder.cu:18
-constexpr float kScaleEps = 0.001953125f;  // reorder.cu:19
-
-struct QuantParams {
-  const uint16_t *x;     // bf16 [M, KQ]
-  const int16_t *idx;    // [KQ]
-  const uint16_t *w;     // rmsnorm weight bf16 [KQ] (RMS only)
-  uint8_t *q;            // [M, K/2]
-  uint8_t *sf;           // swizzled scale bytes
-  float eps;
-  int M, KQ, KE;
-  int num_tiles;
-};
-
-template <int R> struct TileMap;  // local row lr of tile t -> row inside the 128-row block; w0 = first SF word
-template <> struct TileMap<8> {
-  static __device__ __forceinline__ int row(int t, int lr) { return 32 * (lr & 3) + 2 * t + (lr >> 2); }
-  static __device__ __forceinline__ int w0(int t) { return 8 * t; }
-};
-template <> struct TileMap<4> {
-  static __device__ __forceinline__ int row(int t, int lr) { return 32 * lr + t; }
-  static __device__ __forceinline__ int w0(int t) { return 4 * t; }
-};
-template <> struct TileMap<2> {
-  static __device__ __forceinline__ int row(int t, int lr) { return 32 * (2 * (t >> 5) + lr) + (t & 31); }
-  static __device__ __forceinline__ int w0(int t) { return 4 * (t & 31) + 2 * (t >> 5); }
-};
-template <> struct TileMap<1> {
-  static __device__ __forceinline__ int row(int t, int) { return t; }
-  static __device__ __forceinline__ int w0(int t) { return 4 * (t & 31) + (t >> 5); }
-};
-
-// position (in units of one channel chunk = 2R bytes) of channel c inside the staged tile
-template <int R> __device__ __forceinline__ int chan_pos(int c) {
-  if constexpr (R == 1) return c;
-  else return c ^ ((c >> 3) & (64 / R - 1));
-}
-
 // Primary quantisation of 16 values (reorder.cu:127-165): returns the E4M3 byte, the two code words,
 // the decoded scale sf and the unrounded clamped scale s.
 __device__ __forceinline__ uint32_t quant16(const float (&x)[16], uint32_t &c_lo, uint32_t &c_hi, float &sf,
@@ -333,8 +295,18 @@ static int check_common(const void *x, int64_t M, int KQ, const void *idx, int K
   return ARCQ_OK;
 }
 
+// ARCQ_QUANT_V=1 forces the single-role kernel of this file (experiments); default is the warp-specialised family
+static bool use_ws() {
+  static const int v = getenv("ARCQ_QUANT_V") ? atoi(getenv("ARCQ_QUANT_V")) : 2;
+  return v != 1;
+}
+
 template <bool IS_W>
 static int dispatch_quant(const QuantParams &p, int flavour, cudaStream_t st) {
+  if (use_ws()) {
+    const int rc = launch_quant_ws(p, flavour, IS_W, false, st);
+    if (rc != ARCQ_ENOSUP) return rc;
+  }
   const int R = pick_rows(p.KQ, p.KE, false);
 #define ARCQ_CASE(RR)                                                                      \
   case RR:                                                                                 \
@@ -397,6 +369,10 @@ extern "C" int arcq_rmsnorm_quantize_x(const void *x, const void *w, float eps, 
   if (M == 0) return ARCQ_OK;
   QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, eps, (int)M, H, KE, 0};
   cudaStream_t st = (cudaStream_t)stream;
+  if (use_ws()) {
+    const int rc = launch_quant_ws(p, ARCQ_FLAVOUR_16, false, true, st);
+    if (rc != ARCQ_ENOSUP) return rc;
+  }
   switch (pick_rows(H, KE, true)) {
     case 8: return launch_quant<8, 0, false, true>(p, st);
     case 4: return launch_quant<4, 0, false, true>(p, st);

@@ -1,0 +1,51 @@
+// quant.cuh -- parameters shared by the quantise kernel families (quant.cu, quant_ws.cu).
+#pragma once
+#include "common.cuh"
+
+namespace arcq {
+
+struct QuantParams {
+  const uint16_t *x;     // bf16 [M, KQ]
+  const int16_t *idx;    // [KQ]
+  const uint16_t *w;     // rmsnorm weight bf16 [KQ] (RMS only)
+  uint8_t *q;            // [M, K/2]
+  uint8_t *sf;           // swizzled scale bytes
+  float eps;
+  int M, KQ, KE;
+  int num_tiles;
+};
+
+constexpr float kFp4Max = 6.0f;            // reorder.cu:17
+constexpr float kFp8Max = 448.0f;          // reorder.cu:18
+constexpr float kScaleEps = 0.001953125f;  // reorder.cu:19
+
+// local row lr of tile t -> row inside the 128-row scale-factor block; w0 = first 32-bit SF word of the tile's
+// 4R-byte run inside each 512-byte atom (the tcgen05 128x4 layout: byte = (row%32)*16 + (row/32)*4 + g%4)
+template <int R> struct TileMap;
+template <> struct TileMap<8> {
+  static __device__ __forceinline__ int row(int t, int lr) { return 32 * (lr & 3) + 2 * t + (lr >> 2); }
+  static __device__ __forceinline__ int w0(int t) { return 8 * t; }
+};
+template <> struct TileMap<4> {
+  static __device__ __forceinline__ int row(int t, int lr) { return 32 * lr + t; }
+  static __device__ __forceinline__ int w0(int t) { return 4 * t; }
+};
+template <> struct TileMap<2> {
+  static __device__ __forceinline__ int row(int t, int lr) { return 32 * (2 * (t >> 5) + lr) + (t & 31); }
+  static __device__ __forceinline__ int w0(int t) { return 4 * (t & 31) + 2 * (t >> 5); }
+};
+template <> struct TileMap<1> {
+  static __device__ __forceinline__ int row(int t, int) { return t; }
+  static __device__ __forceinline__ int w0(int t) { return 4 * (t & 31) + (t >> 5); }
+};
+
+// position (in units of one channel chunk = 2R bytes) of channel c inside the staged channel-major tile
+template <int R> __device__ __forceinline__ int chan_pos(int c) {
+  if constexpr (R == 1) return c;
+  else return c ^ ((c >> 3) & (64 / R - 1));
+}
+
+// warp-specialised kernel family (quant_ws.cu); returns ARCQ_ENOSUP for shapes it does not take
+int launch_quant_ws(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);
+
+}  // namespace arcq

@@ -1,0 +1,61 @@
+"""Quantise-kernel timing / profiling driver (GPU box).
+
+  python scripts/quant_prof.py [--shapes M,KQ,KE ...] [--iters 20] [--rms]
+Prints one line per shape: us, algorithmic GB/s (SURVEY.md §8d bytes), fraction of MEASURED_PEAKS hbm_gbs.
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from arcquant_b200 import agemm  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shapes", nargs="*", default=["8192,4096,256", "8192,14336,512", "8192,3584,256", "8192,18944,512",
+                                                    "8192,28672,1024", "8192,8192,512", "2048,4096,256", "512,4096,256"])
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--rms", action="store_true")
+    args = ap.parse_args()
+    peak = 6540.0
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        peak = json.load(open(p))["hbm_gbs"]
+    dev = torch.device("cuda:0")
+    for sh in args.shapes:
+        M, KQ, KE = [int(v) for v in sh.split(",")]
+        g = torch.Generator().manual_seed(KQ)
+        # several distinct input buffers so consecutive launches do not hit in the 126 MB L2
+        nbuf = max(2, int(400e6 // (M * KQ * 2)) + 1)
+        xs = [(torch.randn(M, KQ, generator=g) * 50).to(torch.bfloat16).to(dev) for _ in range(min(nbuf, 8))]
+        idx = torch.randperm(KQ, generator=g).to(torch.int16).to(dev)
+        w = torch.ones(KQ, dtype=torch.bfloat16, device=dev)
+        rms = args.rms and 2048 <= KQ <= 8192
+
+        def run(x):
+            if rms:
+                return agemm.rmsnorm_quantize_x(x, w, 1e-6, idx, KE)
+            return agemm.reorder_quantize_x(x, idx, KE)
+        for i in range(3):
+            run(xs[i % len(xs)])
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.iters):
+            run(xs[i % len(xs)])
+        e1.record()
+        torch.cuda.synchronize()
+        us = 1e3 * e0.elapsed_time(e1) / args.iters
+        by = M * (2 * KQ + (KQ + KE) // 2 + (KQ + KE) // 16) + 2 * KQ
+        gbs = by / us / 1e3
+        print("quant%s M=%d KQ=%d KE=%d: %.1f us  %.0f GB/s  %.3f of measured %.0f" % (
+            "+rms" if rms else "", M, KQ, KE, us, gbs, gbs / peak, peak), flush=True)
+
+
+if __name__ == "__main__":
+    main()

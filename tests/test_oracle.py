@@ -229,3 +229,26 @@ def test_oracle_rejects_bad_shapes(O):
     x = np.zeros((2, 100), dtype=np.uint16)
     with pytest.raises(ValueError):
         O.quantize_x(x, np.arange(100, dtype=np.int16), 0, 0)
+
+
+def test_div6_exact():
+    """The kernels' division-free amax/6 (q0 = a*r6; rem = fma(-6, q0, a); q = fma(rem, r6, q0), quant_ws.cu div6) is
+    bit-identical to the correctly rounded fp32 division (reorder.cu:138) for EVERY finite non-negative bf16 amax."""
+    from fractions import Fraction
+
+    def rn32(fr):
+        if fr == 0:
+            return np.float32(0)
+        f = np.float32(float(fr))
+        cands = [np.nextafter(f, np.float32(-np.inf)), f, np.nextafter(f, np.float32(np.inf))]
+        return np.float32(min(cands, key=lambda c: (abs(Fraction(float(c)) - fr), int(np.float32(c).view(np.uint32)) & 1)))
+
+    r6 = np.float32(1.0) / np.float32(6.0)
+    assert int(r6.view(np.uint32)) == 0x3E2AAAAB
+    R = Fraction(float(r6))
+    for h in list(range(0, 0x7F80, 7)) + list(range(0x4000, 0x4600)):
+        a = Fraction(float(np.array([h << 16], dtype=np.uint32).view(np.float32)[0]))
+        q0 = Fraction(float(rn32(a * R)))
+        rem = Fraction(float(rn32(a - 6 * q0)))
+        q = rn32(q0 + rem * R)
+        assert q.view(np.uint32) == rn32(a / 6).view(np.uint32), hex(h)
