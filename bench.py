@@ -149,16 +149,29 @@ def run_reference(args):
     }))
 
 
-class Layer:
-    """Device-resident state of one Llama-3-8B layer's linears: quantised weights + activation buffers."""
+ROW_PARALLEL = ("o", "down")  # K-split + all-reduce; the others are N-split
 
-    def __init__(self, torch, agemm, M, dev, seed=0):
+
+class Layer:
+    """Device-resident state of one Llama-3-8B layer's linears: quantised weights + activation buffers.
+    world > 1: this rank's tensor-parallel shard (arcquant_b200/tp.py): qkv and gate/up split N, o and down split K by
+    channel ownership with their ARC columns and are followed by an all-reduce of the bf16 partials."""
+
+    def __init__(self, torch, agemm, M, dev, seed=0, world=1, rank=0):
         from tests._util import make_acts
-        self.torch, self.agemm, self.M = torch, agemm, M
+        from arcquant_b200 import tp
+        self.torch, self.agemm, self.M, self.world = torch, agemm, M, world
         self.items = []
         g = torch.Generator().manual_seed(seed)
         for name, KQ, KE, Ns in LLAMA3_8B_LAYER:
             xs, idx = make_acts(min(M, 256), KQ, KE, seed=seed + KQ)  # distribution A, pre-scaled
+            row = name in ROW_PARALLEL and world > 1
+            if row:
+                lo, hi = tp.split_rows(KQ, world, rank, 64)
+                idx, KE = tp.shard_reorder_index(idx, KE, world, rank)
+                xs, KQ = xs[:, lo:hi].contiguous(), hi - lo
+            elif world > 1:
+                Ns = [n // world for n in Ns]
             reps = (M + xs.shape[0] - 1) // xs.shape[0]
             x_host = xs.repeat(reps, 1)[:M].contiguous()
             # de-correlate repeated blocks cheaply: flip signs per row block
@@ -171,7 +184,7 @@ class Layer:
                 sw = w.max().float() / (448.0 * 6.0)
                 qw, sfw = agemm.reorder_quantize_w((w / sw).to(torch.bfloat16).to(dev), idx_d, KE)
                 ws.append((N, qw, sfw, float(sw)))
-            self.items.append({"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host,
+            self.items.append({"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host, "reduce": row,
                                "x": x_host.to(dev), "w": ws,
                                "y": [torch.empty((M, N), dtype=torch.bfloat16, device=dev) for N in Ns],
                                "y_host": [torch.empty((M, N), dtype=torch.bfloat16).pin_memory() for N in Ns]})
@@ -194,6 +207,8 @@ class Layer:
                 if events is not None:
                     e1 = self.torch.cuda.Event(enable_timing=True); e1.record()
                     events.append(("gemm", it["KQ"], it["KE"], N, e0, e1))
+                if it["reduce"]:
+                    self.dist.all_reduce(y)
 
     def step_e2e(self):
         """Same step through the public API with host buffers: H2D of every activation, D2H of every result."""
@@ -203,7 +218,15 @@ class Layer:
             qx, sfx = ag.reorder_quantize_x(x, it["idx"], it["KE"])
             for (N, qw, sfw, sw), y, yh in zip(it["w"], it["y"], it["y_host"]):
                 ag.matmul(qx, qw, sfx, sfw, sw, out=y)
+                if it["reduce"]:
+                    self.dist.all_reduce(y)
                 yh.copy_(y, non_blocking=True)
+
+    def flops(self):
+        return sum(2.0 * self.M * N * (it["KQ"] + it["KE"]) for it in self.items for (N, _, _, _) in it["w"])
+
+    def allreduce_bytes(self):
+        return sum(y.numel() * 2 for it in self.items if it["reduce"] for y in it["y"])
 
     def e2e_bytes(self):
         h2d = sum(it["x_host"].numel() * 2 for it in self.items)
@@ -226,7 +249,9 @@ def run_native(args):
     from arcquant_b200 import agemm
     peaks = load_peaks()
     M = args.tokens
-    layer = Layer(torch, agemm, M, dev)
+    tp_mode = world > 1 and args.parallelism == "tp"
+    layer = Layer(torch, agemm, M, dev, world=world if tp_mode else 1, rank=rank if tp_mode else 0)
+    layer.dist = dist
 
     def barrier():
         if world > 1:
@@ -254,8 +279,11 @@ def run_native(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t.item())
-    flops = layer_flops(M)
-    value = world * flops * args.steps / (ms_max * 1e-3) / 1e12
+    ft = torch.tensor([layer.flops()], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ft)  # whole-job FLOPs of one step: sum of the ranks' shards (TP) or replicas
+    flops_job = float(ft.item())
+    value = flops_job * args.steps / (ms_max * 1e-3) / 1e12
 
     # ---- e2e: host activations in, results out, inside the timed region ----
     for _ in range(2):
@@ -269,19 +297,19 @@ def run_native(args):
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_val = world * flops * args.e2e_steps / (float(t.item()) * 1e-3) / 1e12
+    e2e_val = flops_job * args.e2e_steps / (float(t.item()) * 1e-3) / 1e12
     h2d, d2h = layer.e2e_bytes()
 
+    # ---- per-kernel averages (instrumented pass: CUDA events around every launch, same stream; every rank runs it
+    # because the row-parallel layers all-reduce) ----
+    events = []
+    for _ in range(args.steps):
+        layer.step(events)
+    barrier()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-
-    # ---- per-kernel averages (instrumented pass: CUDA events around every launch, same stream) ----
-    events = []
-    for _ in range(args.steps):
-        layer.step(events)
-    torch.cuda.synchronize()
     per = {}
     for kind, KQ, KE, N, a, b in events:
         per.setdefault((kind, KQ, KE, N), []).append(a.elapsed_time(b))
@@ -330,15 +358,18 @@ def run_native(args):
 
     out = {
         "metric": "nvfp4_arc_linear_tflops", "value": value, "unit": "TFLOP/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+        "scaling": "strong" if tp_mode else "weak",
         "vs_baseline": None, "dtype": "nvfp4 (e2m1 x e2m1, ue4m3 block scales, fp32 accumulate, bf16 out)",
         "data": "synthetic",
         "config": {"workload": "llama3-8b decoder-layer linears (qkv, o, gate/up, down): 4 x reorder+NVFP4+ARC quantize "
-                               "+ 7 x block-scaled GEMM per step", "tokens_per_gpu": M,
+                               "+ 7 x block-scaled GEMM per step", "tokens_per_gpu": M, "tokens_global": M if tp_mode else M * world,
                    "select_num": {n: ke for n, _, ke, _ in LLAMA3_8B_LAYER},
                    "l2": "inputs larger than L2 (per-step working set > 1 GB vs 126 MB L2); no flush needed",
-                   "parallelism": "replicas (token-parallel), no collective" if world > 1 else "single GPU"},
-        "tokens_per_s_linear_path": world * M * args.steps / (ms_max * 1e-3),
+                   "parallelism": ("tp%d: qkv/gate/up column-parallel, o/down row-parallel (ARC columns with their shard) + NCCL "
+                                   "all-reduce of %d bf16 bytes per step" % (world, layer.allreduce_bytes())) if tp_mode
+                   else ("replicas (token-parallel), no collective" if world > 1 else "single GPU")},
+        "tokens_per_s_linear_path": (M if tp_mode else world * M) * args.steps / (ms_max * 1e-3),
         "e2e": {"value": e2e_val, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": args.e2e_steps},
         "gpu_launches": int(launches),
@@ -357,6 +388,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--tokens", type=int, default=8192, help="M: rows (tokens) per GPU per step")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--parallelism", default="tp", choices=["tp", "replicas"],
+                    help="N>1: tensor-parallel shards of one layer (default, north star) or independent token replicas")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-tokens", type=int, default=512)
     ap.add_argument("--cpu-reps", type=int, default=8)
