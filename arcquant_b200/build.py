@@ -15,7 +15,7 @@ _ROOT = os.path.dirname(_HERE)
 CSRC = os.path.join(_HERE, "csrc")
 INCLUDE = os.path.join(_ROOT, "include")
 LIB = os.path.join(_HERE, "libarcq_b200.so")
-SOURCES = ["runtime.cu", "quant.cu", "quant_ws.cu", "gemm.cu", "gemm_cluster.cu", "gemm_pair.cu"]
+SOURCES = ["runtime.cu", "quant.cu", "quant_ws.cu", "quant_tma.cu", "gemm.cu", "gemm_cluster.cu", "gemm_pair.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-I" + INCLUDE, "-I" + CSRC,

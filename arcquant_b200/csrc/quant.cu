@@ -296,13 +296,19 @@ static int check_common(const void *x, int64_t M, int KQ, const void *idx, int K
 }
 
 // ARCQ_QUANT_V=1 forces the single-role kernel of this file (experiments); default is the warp-specialised family
-static bool use_ws() {
-  static const int v = getenv("ARCQ_QUANT_V") ? atoi(getenv("ARCQ_QUANT_V")) : 2;
-  return v != 1;
+static int quant_version() {
+  static const int v = getenv("ARCQ_QUANT_V") ? atoi(getenv("ARCQ_QUANT_V")) : 3;
+  return v;
 }
+static bool use_ws() { return quant_version() == 2; }
+static bool use_tma() { return quant_version() == 3; }
 
 template <bool IS_W>
 static int dispatch_quant(const QuantParams &p, int flavour, cudaStream_t st) {
+  if (use_tma()) {
+    const int rc = launch_quant_tma(p, flavour, IS_W, false, st);
+    if (rc != ARCQ_ENOSUP) return rc;
+  }
   if (use_ws()) {
     const int rc = launch_quant_ws(p, flavour, IS_W, false, st);
     if (rc != ARCQ_ENOSUP) return rc;
@@ -369,6 +375,10 @@ extern "C" int arcq_rmsnorm_quantize_x(const void *x, const void *w, float eps, 
   if (M == 0) return ARCQ_OK;
   QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, eps, (int)M, H, KE, 0};
   cudaStream_t st = (cudaStream_t)stream;
+  if (use_tma()) {
+    const int rc = launch_quant_tma(p, ARCQ_FLAVOUR_16, false, true, st);
+    if (rc != ARCQ_ENOSUP) return rc;
+  }
   if (use_ws()) {
     const int rc = launch_quant_ws(p, ARCQ_FLAVOUR_16, false, true, st);
     if (rc != ARCQ_ENOSUP) return rc;

@@ -46,6 +46,8 @@ template <int R> __device__ __forceinline__ int chan_pos(int c) {
 }
 
 // warp-specialised kernel family (quant_ws.cu); returns ARCQ_ENOSUP for shapes it does not take
+// TMA-staged kernel family (quant_tma.cu); same contract
+int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);
 int launch_quant_ws(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);
 
 }  // namespace arcq

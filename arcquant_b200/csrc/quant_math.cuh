@@ -1,0 +1,82 @@
+// quant_math.cuh -- the arithmetic of one 16-group shared by the quantise kernel families.
+#pragma once
+#include "quant.cuh"
+
+namespace arcq {
+
+// amax / 6 correctly rounded without the division subroutine (Markstein: q' = RN(q0 + RN(a - 6 q0) * r))
+static __device__ __forceinline__ float div6(float a) {
+  const float r6 = 0.16666667163372039794921875f;  // RN(1/6) = 0x3e2aaaab
+  const float q0 = __fmul_rn(a, r6);
+  const float rem = __fmaf_rn(-6.0f, q0, a);
+  return __fmaf_rn(rem, r6, q0);
+}
+
+// eight e2m1 codes (one word, element 0 in the low nibble) -> four f16x2 (element 2b in the low half): exact
+static __device__ __forceinline__ void e2m1x8_to_f16x2(uint32_t w, uint32_t (&d)[4]) {
+  asm("{\n\t"
+      ".reg .b8 b0, b1, b2, b3;\n\t"
+      "mov.b32 {b0, b1, b2, b3}, %4;\n\t"
+      "cvt.rn.f16x2.e2m1x2 %0, b0;\n\t"
+      "cvt.rn.f16x2.e2m1x2 %1, b1;\n\t"
+      "cvt.rn.f16x2.e2m1x2 %2, b2;\n\t"
+      "cvt.rn.f16x2.e2m1x2 %3, b3;\n\t"
+      "}"
+      : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+      : "r"(w));
+}
+
+// primary quantisation of 16 values (reorder.cu:127-165): returns the E4M3 byte; s = unrounded clamped scale
+static __device__ __forceinline__ uint32_t quant16(const float (&x)[16], const float *rcp_lut, uint32_t &c_lo, uint32_t &c_hi,
+                                            float &s) {
+  float amax = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(x[i]));
+  s = fmaxf(kScaleEps, fminf(kFp8Max, div6(amax)));  // :138
+  const uint32_t sfb = f32_to_e4m3(s);               // :143
+  const float r = rcp_lut[sfb];                      // RN(1/sf), :146
+  float t[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) t[i] = __fmul_rn(x[i], r);  // :153-156
+  c_lo = f32x8_to_e2m1(t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7]);
+  c_hi = f32x8_to_e2m1(t[8], t[9], t[10], t[11], t[12], t[13], t[14], t[15]);
+  return sfb;
+}
+
+// residual of 16 values: e = bf16(x - deq(code) * sub) (reorder.cu:157-160 / :474), then quantised again
+static __device__ __forceinline__ uint32_t residual16(const float (&x)[16], uint32_t c_lo, uint32_t c_hi, float sub,
+                                               const float *rcp_lut, uint32_t &r_lo, uint32_t &r_hi) {
+  float e[16];
+#ifndef ARCQ_E2M1_CVT_DECODE  // cvt.rn.f16x2.e2m1x2 decoded differently from the arithmetic decode on B200 (r1c_debug.log)
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const uint32_t code = ((i < 8 ? c_lo : c_hi) >> (4 * (i & 7))) & 0xfu;
+    e[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmaf_rn(-e2m1_to_f32(code), sub, x[i])));
+  }
+#else
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t d[4];
+    e2m1x8_to_f16x2(h ? c_hi : c_lo, d);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&d[b]));  // exact
+      e[8 * h + 2 * b] = bf16lo_to_f32(f32_to_bf16_bits(__fmaf_rn(-f.x, sub, x[8 * h + 2 * b])));
+      e[8 * h + 2 * b + 1] = bf16lo_to_f32(f32_to_bf16_bits(__fmaf_rn(-f.y, sub, x[8 * h + 2 * b + 1])));
+    }
+  }
+#endif
+  float s2;
+  return quant16(e, rcp_lut, r_lo, r_hi, s2);
+}
+
+// R rows (2R bytes) of one channel chunk
+template <int R> static __device__ __forceinline__ void lds_chunk(const uint8_t *src, uint32_t (&v)[(R + 1) / 2]) {
+  if constexpr (R == 8) { const uint4 q = *reinterpret_cast<const uint4 *>(src); v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w; }
+  else if constexpr (R == 4) { const uint2 q = *reinterpret_cast<const uint2 *>(src); v[0] = q.x; v[1] = q.y; }
+  else if constexpr (R == 2) v[0] = *reinterpret_cast<const uint32_t *>(src);
+  else v[0] = *reinterpret_cast<const uint16_t *>(src);
+}
+
+
+}  // namespace arcq

@@ -1,0 +1,452 @@
+// quant_tma.cu -- TMA-staged reorder + NVFP4 + ARC quantise kernel (sm_100a).
+//
+// Same arithmetic contract and output layout as quant.cu (reference
+// kernels/src/{reorder,down,rmsnorm}.cu).  Organisation:
+//
+//  * persistent CTAs (two per SM when the tile is small enough); a work item is R rows of one 128-row scale block;
+//  * ONE thread streams whole bf16 rows into a ring of row-major staging slots with cp.async.bulk (TMA, mbarrier
+//    complete_tx): the next tile(s) are in flight while the current one is quantised, with no registers tied up;
+//  * all threads transpose a landed slot (LDS.128 -> PRMT -> swizzled STS) into the channel-major tile
+//    ("[channel][R rows]") so the permuted gather is one 2R-byte shared load per channel for all R rows;
+//  * gather offsets come from a once-per-CTA table built from reorder_index; when a thread owns the same 16-group
+//    in every tile (KQ/16 <= threads) its 16 offsets live in registers for the whole kernel;
+//  * phase A = primary quantisation (one group x R rows per thread), phase B = ARC residuals spread over all
+//    threads as (group,row) items; amax/6 by exact FMA division, RN(1/sf) and sf from a 127-entry LUT;
+//  * scale bytes are assembled per tile in shared memory and leave as whole 4R-byte runs of the 128x4 layout.
+#include "quant.cuh"
+#include "quant_math.cuh"
+#include "ptx.cuh"
+#include <stdlib.h>
+
+namespace arcq {
+namespace {
+
+struct CarveT {  // shared-memory layout (bytes), computed identically on host and device
+  int lut, sfs, arc, tab, wtab, part, rstd, tile, stage, total;
+};
+__host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool tab32, int S) {
+  CarveT c;
+  int o = 128;                  // mbarriers full[S] (S <= 4)
+  c.lut = o; o += 2 * 128 * 4;  // rcp + sf LUTs
+  c.sfs = o; o += 2 * ((KQ + KE) / 64) * 4 * R;  // two scale staging buffers [chunk][lr][slot%4]
+  o = (o + 15) & ~15;
+  c.arc = o; o += (KE / 16) * R * 48;            // per ARC (group,row): 16 bf16 x, 2 code words, subtrahend scale
+  c.tab = o; o += KQ * (tab32 ? 4 : 2);
+  o = (o + 15) & ~15;
+  c.wtab = o; if (rms) o += KQ * 2;
+  o = (o + 15) & ~15;
+  c.part = o; if (rms) o += R * 512 * 4;
+  c.rstd = o; if (rms) o += 64;
+  o = (o + 127) & ~127;
+  c.tile = o; o += KQ * 2 * R;
+  c.stage = o; o += S * KQ * 2 * R;
+  c.total = o;
+  return c;
+}
+
+template <int R, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantParams p, const int S) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int CB = 2 * R;        // bytes of one channel chunk
+  constexpr int RP = (R + 1) / 2;  // 32-bit words per chunk
+  constexpr int TPB = 128 / R;     // tiles per 128-row block
+  static_assert(!(OWN && TAB32), "owned groups convert the 16-bit table once");
+  const int KQ = p.KQ, KE = p.KE, K = KQ + KE;
+  const int G = (KQ - KE) / 16, ngroups = KQ / 16, nunits = KQ / 8, nchunks = K / 64;
+  const CarveT cv = carve_t(R, KQ, KE, RMS, TAB32, S);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem);
+  float *rcp_lut = reinterpret_cast<float *>(smem + cv.lut), *sf_lut = rcp_lut + 128;
+  const int sfs_bytes = nchunks * 4 * R;
+  uint8_t *arcs = smem + cv.arc;
+  uint8_t *tile = smem + cv.tile;
+  uint8_t *stage = smem + cv.stage;
+  const uint32_t rowbytes = (uint32_t)KQ * 2;
+  const int tile_bytes = KQ * CB;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  float *part = reinterpret_cast<float *>(smem + cv.part), *rstd_s = reinterpret_cast<float *>(smem + cv.rstd);
+  const uint16_t *wtab = reinterpret_cast<const uint16_t *>(smem + cv.wtab);
+
+  // one thread streams the rows of tile `tile_id` into staging slot s
+  auto issue_tile = [&](int s, int tile_id) {
+    const int blk = tile_id / TPB, t = tile_id % TPB;
+    const int r0 = blk * 128 + TileMap<R>::row(t, 0);
+    const int mrows = p.M - r0;
+    int nv = 0;
+#pragma unroll
+    for (int lr = 0; lr < R; ++lr) nv += TileMap<R>::row(0, lr) < mrows ? 1 : 0;
+    ptx::mbar_arrive_expect_tx(&full[s], (uint32_t)nv * rowbytes);
+    const uint8_t *src = reinterpret_cast<const uint8_t *>(p.x) + (int64_t)r0 * rowbytes;
+    uint8_t *dst = stage + (size_t)s * tile_bytes;
+#pragma unroll
+    for (int lr = 0; lr < R; ++lr)
+      if (TileMap<R>::row(0, lr) < mrows)
+        ptx::bulk_load(dst + (size_t)lr * rowbytes, src + (size_t)TileMap<R>::row(0, lr) * rowbytes, rowbytes, &full[s]);
+  };
+
+  // ---- one-time setup: barriers, LUTs, gather-offset table ----
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) ptx::mbar_init(&full[s], 1);
+    ptx::fence_barrier_init();
+  }
+  if (p.M % 128) {  // a ragged last block leaves rows of some slots unwritten: give them defined (zero) content
+    for (int i = tid; i < S * tile_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
+    ptx::fence_proxy_async();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      const int tl = blockIdx.x + s * gridDim.x;
+      if (tl < p.num_tiles) issue_tile(s, tl);
+    }
+  }
+  if (tid < 128) {
+    const float sf = e4m3_to_f32(tid < 127 ? tid : 126);
+    sf_lut[tid] = sf;
+    rcp_lut[tid] = __frcp_rn(sf);  // == f32(1.0 / (double)sf) for every E4M3 value (reorder.cu:146)
+  }
+  for (int u = tid; u < nunits; u += THREADS) {
+    const uint4 w4 = __ldg(reinterpret_cast<const uint4 *>(p.idx) + u);
+    const uint32_t ww[4] = {w4.x, w4.y, w4.z, w4.w};
+    uint32_t pos[8];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      pos[2 * i] = (uint32_t)chan_pos<R>((int)(ww[i] & 0xffffu));
+      pos[2 * i + 1] = (uint32_t)chan_pos<R>((int)(ww[i] >> 16));
+    }
+    if constexpr (TAB32) {
+      uint4 *dst = reinterpret_cast<uint4 *>(smem + cv.tab) + 2 * u;
+      dst[0] = make_uint4(pos[0] * CB, pos[1] * CB, pos[2] * CB, pos[3] * CB);
+      dst[1] = make_uint4(pos[4] * CB, pos[5] * CB, pos[6] * CB, pos[7] * CB);
+    } else {
+      reinterpret_cast<uint4 *>(smem + cv.tab)[u] =
+          make_uint4(pos[0] | (pos[1] << 16), pos[2] | (pos[3] << 16), pos[4] | (pos[5] << 16), pos[6] | (pos[7] << 16));
+    }
+    if constexpr (RMS) {  // rmsnorm weight in reordered order
+      uint32_t wv[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        wv[2 * i] = __ldg(p.w + (ww[i] & 0xffffu));
+        wv[2 * i + 1] = __ldg(p.w + (ww[i] >> 16));
+      }
+      reinterpret_cast<uint4 *>(smem + cv.wtab)[u] =
+          make_uint4(wv[0] | (wv[1] << 16), wv[2] | (wv[3] << 16), wv[4] | (wv[5] << 16), wv[6] | (wv[7] << 16));
+    }
+  }
+  __syncthreads();
+
+  // gather offsets (bytes into the tile) of the 16 channels of group g
+  auto load_offsets = [&](int g, uint32_t(&off)[16]) {
+    if constexpr (TAB32) {
+      const uint4 *t4 = reinterpret_cast<const uint4 *>(smem + cv.tab) + 4 * g;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { const uint4 w = t4[q]; off[4 * q] = w.x; off[4 * q + 1] = w.y; off[4 * q + 2] = w.z; off[4 * q + 3] = w.w; }
+    } else {
+      const uint4 *t4 = reinterpret_cast<const uint4 *>(smem + cv.tab) + 2 * g;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const uint4 w = t4[q];
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { off[8 * q + 2 * i] = (ww[i] & 0xffffu) * CB; off[8 * q + 2 * i + 1] = (ww[i] >> 16) * CB; }
+      }
+    }
+  };
+  auto load_w = [&](int g, float(&wf)[16]) {
+    const uint4 *t4 = reinterpret_cast<const uint4 *>(wtab) + 2 * g;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const uint4 w = t4[q];
+      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { wf[8 * q + 2 * i] = bf16lo_to_f32(ww[i]); wf[8 * q + 2 * i + 1] = bf16hi_to_f32(ww[i]); }
+    }
+  };
+  auto slots = [&](int g, int &slot_p, int &slot_r) {
+    slot_p = g; slot_r = g;
+    if (g >= G) {
+      const int j = g - G;
+      if constexpr (FLAVOUR == 0) { slot_p = G + 2 * j; slot_r = slot_p + 1; }  // reorder.cu:139,175
+      else { slot_p = G + 4 * (j >> 1) + (j & 1); slot_r = slot_p + 2; }        // reorder.cu:451-463,510-515
+    }
+  };
+
+  uint32_t own_off[OWN ? 16 : 1];
+  if constexpr (OWN) load_offsets(tid < ngroups ? tid : 0, own_off);
+
+  // scale bytes of one finished tile leave as contiguous 4R-byte runs of the swizzled layout
+  auto copy_out_sf = [&](int buf, int blk, int t) {
+    const uint8_t *sfs = smem + cv.sfs + buf * sfs_bytes;
+    uint8_t *dst0 = p.sf + (int64_t)blk * nchunks * 512 + TileMap<R>::w0(t) * 4;
+    for (int c = tid; c < nchunks; c += THREADS) {
+      uint8_t *dst = dst0 + (int64_t)c * 512;
+      const uint8_t *src = sfs + c * (4 * R);
+      if constexpr (R == 8) {
+        reinterpret_cast<uint4 *>(dst)[0] = reinterpret_cast<const uint4 *>(src)[0];
+        reinterpret_cast<uint4 *>(dst)[1] = reinterpret_cast<const uint4 *>(src)[1];
+      } else if constexpr (R == 4) {
+        *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
+      } else if constexpr (R == 2) {
+        *reinterpret_cast<uint2 *>(dst) = *reinterpret_cast<const uint2 *>(src);
+      } else {
+        *reinterpret_cast<uint32_t *>(dst) = *reinterpret_cast<const uint32_t *>(src);
+      }
+    }
+  };
+
+  int n = 0, prev_blk = 0, prev_t = 0;
+  for (int tile_id = blockIdx.x; tile_id < p.num_tiles; tile_id += gridDim.x, ++n) {
+    const int s = n % S;
+    const int blk = tile_id / TPB, t = tile_id % TPB;
+    const int r0 = blk * 128 + TileMap<R>::row(t, 0);
+    const int mrows = p.M - r0;  // row lr of this tile exists iff row(0, lr) < mrows
+    const uint32_t khalf = (uint32_t)K / 2;
+    uint8_t *qbase = p.q + (int64_t)r0 * khalf;
+    uint8_t *sfs = smem + cv.sfs + (n & 1) * sfs_bytes;
+    ptx::mbar_wait(&full[s], (uint32_t)(n / S) & 1u);
+
+    // ---- transpose the landed rows into the channel-major tile ----
+    {
+      const uint8_t *src = stage + (size_t)s * tile_bytes;
+      for (int u = tid; u < nunits; u += THREADS) {
+        uint4 in[R];
+#pragma unroll
+        for (int lr = 0; lr < R; ++lr) in[lr] = *reinterpret_cast<const uint4 *>(src + (size_t)lr * rowbytes + (size_t)u * 16);
+        if constexpr (R == 1) {
+          reinterpret_cast<uint4 *>(tile)[u] = in[0];
+        } else {
+          const uint32_t u8 = (uint32_t)u * 8, um = (uint32_t)u & (64 / R - 1);  // chan_pos(8u + c) = (8u | c) ^ um
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint32_t out[RP];
+#pragma unroll
+            for (int pr = 0; pr < RP; ++pr) {
+              const uint32_t a = (&in[2 * pr].x)[c >> 1], b = (&in[2 * pr + 1].x)[c >> 1];
+              out[pr] = __byte_perm(a, b, (c & 1) ? 0x7632 : 0x5410);
+            }
+            uint8_t *dst = tile + ((u8 | c) ^ um) * CB;
+            if constexpr (R == 8) *reinterpret_cast<uint4 *>(dst) = make_uint4(out[0], out[1], out[2], out[3]);
+            else if constexpr (R == 4) *reinterpret_cast<uint2 *>(dst) = make_uint2(out[0], out[1]);
+            else *reinterpret_cast<uint32_t *>(dst) = out[0];
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {  // slot s has been read by everyone: refill it with the tile S steps ahead
+      const int tl = tile_id + S * gridDim.x;
+      if (tl < p.num_tiles) issue_tile(s, tl);
+    }
+    // every thread has finished phase B of the previous tile (it passed the barrier above): its scale bytes are complete
+    if (n > 0) copy_out_sf((n - 1) & 1, prev_blk, prev_t);
+
+    // ---- rmsnorm: sum of squares in the reference's exact order (rmsnorm.cu:113-157) ----
+    if constexpr (RMS) {
+      const int bdx = KQ / 16;
+      for (int tt = tid; tt < 512; tt += THREADS) {
+        float acc[R];
+#pragma unroll
+        for (int lr = 0; lr < R; ++lr) acc[lr] = 0.0f;
+        if (tt < bdx) {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int c = half * 8 * bdx + 8 * tt + i;
+              uint32_t v[RP];
+              lds_chunk<R>(tile + (size_t)chan_pos<R>(c) * CB, v);
+#pragma unroll
+              for (int lr = 0; lr < R; ++lr) {
+                const float f = (lr & 1) ? bf16hi_to_f32(v[lr >> 1]) : bf16lo_to_f32(v[lr >> 1]);
+                acc[lr] = __fmaf_rn(f, f, acc[lr]);
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int lr = 0; lr < R; ++lr) part[lr * 512 + tt] = acc[lr];
+      }
+      __syncthreads();
+      if (warp < R) {  // one warp replays the reference's tree for one row (rmsnorm.cu:131-154)
+        float *sp = part + warp * 512;
+        for (int k = 0; k < 8; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 256];
+        __syncwarp();
+        for (int k = 0; k < 4; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 128];
+        __syncwarp();
+        for (int k = 0; k < 2; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 64];
+        __syncwarp();
+        float v = sp[lane] + sp[lane + 32];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+        if (lane == 0) rstd_s[warp] = rsqrtf(__fadd_rn(__fdiv_rn(v, (float)KQ), p.eps));  // :157
+      }
+      __syncthreads();
+    }
+
+    // ---- phase A: permuted gather + primary quantisation, one 16-group x R rows per thread per step ----
+    for (int g = tid; g < ngroups; g += THREADS) {
+      uint32_t v[16][RP];
+      if constexpr (OWN) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) lds_chunk<R>(tile + own_off[i], v[i]);
+      } else {
+        uint32_t off[16];
+        load_offsets(g, off);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) lds_chunk<R>(tile + off[i], v[i]);
+      }
+      float wf[RMS ? 16 : 1];
+      if constexpr (RMS) load_w(g, wf);
+      int slot_p, slot_r;
+      slots(g, slot_p, slot_r);
+      uint8_t *sfp = sfs + (slot_p >> 2) * (4 * R) + (slot_p & 3);
+      const int dslot = slot_r - slot_p;
+      const bool arc = g >= G;
+      uint8_t *qg = qbase + 8 * slot_p;
+#pragma unroll
+      for (int lr = 0; lr < R; ++lr) {
+        float x[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          x[i] = (lr & 1) ? bf16hi_to_f32(v[i][lr >> 1]) : bf16lo_to_f32(v[i][lr >> 1]);
+          if constexpr (RMS)  // rmsnorm.cu:165-171: bf16((x * w) * rstd), left to right
+            x[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmul_rn(__fmul_rn(x[i], wf[i]), rstd_s[lr])));
+        }
+        uint32_t c_lo, c_hi;
+        float sc;
+        const uint32_t sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
+        sfp[4 * lr] = (uint8_t)sfb;
+        if (IS_W && arc) sfp[4 * lr + ((dslot >> 2) * (4 * R) + (dslot & 3))] = (uint8_t)sfb;  // reorder.cu:307-316
+        if (!IS_W && arc) {  // hand the residual work of this (group,row) to phase B: values, codes, subtrahend scale
+          uint4 *a = reinterpret_cast<uint4 *>(arcs + ((g - G) * R + lr) * 48);
+          uint32_t xb[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
+          a[0] = make_uint4(xb[0], xb[1], xb[2], xb[3]);
+          a[1] = make_uint4(xb[4], xb[5], xb[6], xb[7]);
+          // 16-wide: rounded scale (reorder.cu:157); 32-wide: unrounded (reorder.cu:474)
+          a[2] = make_uint4(c_lo, c_hi, __float_as_uint(FLAVOUR == 0 ? sf_lut[sfb] : sc), 0u);
+        }
+        uint8_t *qp = qg + TileMap<R>::row(0, lr) * khalf;
+        if (TileMap<R>::row(0, lr) < mrows) {
+          __stcs(reinterpret_cast<uint2 *>(qp), make_uint2(c_lo, c_hi));
+          if (IS_W && arc) __stcs(reinterpret_cast<uint2 *>(qp + 8 * dslot), make_uint2(c_lo, c_hi));
+        }
+      }
+      if constexpr (OWN) break;  // THREADS >= ngroups: one group per thread, its offsets stay in registers
+    }
+
+    // ---- phase B: ARC residuals, one (group, row) item per thread per step, from the stash of phase A ----
+    if constexpr (!IS_W) {
+      __syncthreads();  // stash complete; also: nobody reads the tile any more (the next transpose may overwrite it)
+      const int nitems = (KE / 16) * R;
+      for (int item = tid; item < nitems; item += THREADS) {
+        const int g = G + item / R, lr = item % R;
+        const uint4 *a = reinterpret_cast<const uint4 *>(arcs + item * 48);
+        const uint4 x0 = a[0], x1 = a[1], cs = a[2];
+        const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        float x[16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { x[2 * i] = bf16lo_to_f32(xb[i]); x[2 * i + 1] = bf16hi_to_f32(xb[i]); }
+        uint32_t r_lo, r_hi;
+        const uint32_t rsfb = residual16(x, cs.x, cs.y, __uint_as_float(cs.z), rcp_lut, r_lo, r_hi);
+        int slot_p, slot_r;
+        slots(g, slot_p, slot_r);
+        sfs[(slot_r >> 2) * (4 * R) + 4 * lr + (slot_r & 3)] = (uint8_t)rsfb;
+        const int dr = TileMap<R>::row(0, lr);
+        if (dr < mrows) __stcs(reinterpret_cast<uint2 *>(qbase + (uint32_t)dr * khalf + 8 * slot_r), make_uint2(r_lo, r_hi));
+      }
+    } else {
+      __syncthreads();
+    }
+    prev_blk = blk; prev_t = t;
+  }
+  if (n > 0) {  // scale bytes of the last tile
+    __syncthreads();
+    copy_out_sf((n - 1) & 1, prev_blk, prev_t);
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+
+constexpr int kSmemPerSm = 227 * 1024;
+
+template <int R, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
+int launch(const QuantParams &p0, int S, cudaStream_t stream) {
+  QuantParams p = p0;
+  auto kern = quant_tma_kernel<R, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB>;
+  const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S).total;
+  static int smem_set = 0;  // per instantiation
+  if (smem > smem_set) {
+    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    smem_set = smem;
+  }
+  const int sms = sm_count();
+  if (sms <= 0) return ARCQ_ECUDA;
+  p.num_tiles = (int)(((int64_t)p.M + 127) / 128) * (128 / R);
+  const int grid = p.num_tiles < sms * MINB ? p.num_tiles : sms * MINB;
+  kern<<<grid, THREADS, smem, stream>>>(p, S);
+  ARCQ_CUDA_TRY(cudaGetLastError());
+  count_launch();
+  return ARCQ_OK;
+}
+
+template <int R, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS>
+int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t st) {
+  if (own) return launch<R, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB>(p, S, st);
+  if (tab32) return launch<R, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB>(p, S, st);
+  return launch<R, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB>(p, S, st);
+}
+
+template <int R, int THREADS, int MINB>
+int launch_kind(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st) {
+  if (rms) return launch_tab<R, THREADS, MINB, 0, false, true>(p, S, tab32, own, st);
+  if (is_w) return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, THREADS, MINB, 1, true, false>(p, S, tab32, own, st)
+                                              : launch_tab<R, THREADS, MINB, 0, true, false>(p, S, tab32, own, st);
+  return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, THREADS, MINB, 1, false, false>(p, S, tab32, own, st)
+                                    : launch_tab<R, THREADS, MINB, 0, false, false>(p, S, tab32, own, st);
+}
+
+struct Cfg { int R, threads, minb, S; };
+
+}  // namespace
+
+int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream) {
+  if (p.KQ % 64 || p.KE % 64) return ARCQ_ENOSUP;  // 4-slot scale chunks must not straddle the plain/ARC boundary
+  const int sms = sm_count();
+  if (sms <= 0) return ARCQ_ECUDA;
+  const int ngroups = p.KQ / 16;
+  const int64_t blocks = ((int64_t)p.M + 127) / 128;
+  const int wide = ngroups > 512 ? 1024 : 512;
+  // tile height, threads per CTA, CTAs per SM, staging slots -- first candidate that fits and gives every SM a tile
+  const Cfg cands[] = {{4, 256, 2, 2}, {4, 512, 1, 2}, {2, 256, 2, 2}, {2, wide, 1, 2}, {2, wide, 1, 1},
+                       {1, wide, 1, 2}, {1, wide, 1, 1}};
+  Cfg c{0, 0, 0, 0};
+  bool tab32 = false, own = false;
+  if (const char *e = getenv("ARCQ_QUANT_TMA")) {  // experiment knob: "R,threads,S" (threads 256 = two CTAs per SM)
+    int r = 0, th = 0, s = 0;
+    if (sscanf(e, "%d,%d,%d", &r, &th, &s) == 3) c = Cfg{r, th, th == 256 ? 2 : 1, s};
+  }
+  if (c.R == 0) {
+    for (const Cfg &k : cands) {
+      if (rms && k.threads < 32 * k.R) continue;
+      const bool o = ngroups <= k.threads;
+      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
+      if (need * k.minb > kSmemPerSm) continue;
+      if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;
+      c = k;
+      break;
+    }
+    if (c.R == 0) return ARCQ_ENOSUP;
+  }
+  own = ngroups <= c.threads;
+  tab32 = !own && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
+  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
+#define ARCQ_T(RR, TH, MB) \
+  if (c.R == RR && c.threads == TH && c.minb == MB) return launch_kind<RR, TH, MB>(p, flavour, is_w, rms, c.S, tab32, own, stream);
+  ARCQ_T(8, 512, 1) ARCQ_T(4, 256, 2) ARCQ_T(4, 512, 1) ARCQ_T(2, 256, 2) ARCQ_T(2, 512, 1) ARCQ_T(2, 1024, 1)
+  ARCQ_T(1, 512, 1) ARCQ_T(1, 1024, 1)
+#undef ARCQ_T
+  return ARCQ_ENOSUP;
+}
+
+}  // namespace arcq
