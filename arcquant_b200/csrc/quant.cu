@@ -351,7 +351,7 @@ extern "C" int arcq_quantize_x(const void *x, int64_t M, int KQ, const int16_t *
   flavour = resolve_flavour(flavour, KQ);
   if (int rc = check_common(x, M, KQ, idx, KE, flavour, qx, sfx)) return rc;
   if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, 0.0f, (int)M, KQ, KE, 0};
+  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, 0.0f, (int)M, KQ, KE, 0, 0};
   return dispatch_quant<false>(p, flavour, (cudaStream_t)stream);
 }
 
@@ -360,7 +360,7 @@ extern "C" int arcq_quantize_w(const void *w, int64_t N, int KQ, const int16_t *
   flavour = resolve_flavour(flavour, KQ);
   if (int rc = check_common(w, N, KQ, idx, KE, flavour, qw, sfw)) return rc;
   if (N == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)w, idx, nullptr, (uint8_t *)qw, (uint8_t *)sfw, 0.0f, (int)N, KQ, KE, 0};
+  QuantParams p{(const uint16_t *)w, idx, nullptr, (uint8_t *)qw, (uint8_t *)sfw, 0.0f, (int)N, KQ, KE, 0, 0};
   return dispatch_quant<true>(p, flavour, (cudaStream_t)stream);
 }
 
@@ -373,7 +373,7 @@ extern "C" int arcq_rmsnorm_quantize_x(const void *x, const void *w, float eps, 
     return ARCQ_ENOSUP;
   }
   if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, eps, (int)M, H, KE, 0};
+  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, eps, (int)M, H, KE, 0, 0};
   cudaStream_t st = (cudaStream_t)stream;
   if (use_tma()) {
     const int rc = launch_quant_tma(p, ARCQ_FLAVOUR_16, false, true, st);

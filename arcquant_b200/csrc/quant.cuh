@@ -13,6 +13,7 @@ struct QuantParams {
   float eps;
   int M, KQ, KE;
   int num_tiles;
+  int debug;  // experiment bits (ARCQ_QUANT_DEBUG): 1 skip transpose, 2 skip gather, 4 skip quantise math, 8 skip residuals
 };
 
 constexpr float kFp4Max = 6.0f;            // reorder.cu:17

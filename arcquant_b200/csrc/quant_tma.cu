@@ -44,12 +44,15 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
   return c;
 }
 
-template <int R, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantParams p, const int S) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int CB = 2 * R;        // bytes of one channel chunk
   constexpr int RP = (R + 1) / 2;  // 32-bit words per chunk
   constexpr int TPB = 128 / R;     // tiles per 128-row block
+  constexpr int RTP = (RT + 1) / 2;  // 32-bit words of the RT rows one thread quantises
+  constexpr int RB = R / RT;         // row blocks per tile: a phase-A item is (16-group, row block)
+  static_assert(R % RT == 0, "row blocks tile the tile");
   static_assert(!(OWN && TAB32), "owned groups convert the 16-bit table once");
   const int KQ = p.KQ, KE = p.KE, K = KQ + KE;
   const int G = (KQ - KE) / 16, ngroups = KQ / 16, nunits = KQ / 8, nchunks = K / 64;
@@ -171,7 +174,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
   };
 
   uint32_t own_off[OWN ? 16 : 1];
-  if constexpr (OWN) load_offsets(tid < ngroups ? tid : 0, own_off);
+  if constexpr (OWN) load_offsets(tid / RB < ngroups ? tid / RB : 0, own_off);
 
   // scale bytes of one finished tile leave as contiguous 4R-byte runs of the swizzled layout
   auto copy_out_sf = [&](int buf, int blk, int t) {
@@ -207,7 +210,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     // ---- transpose the landed rows into the channel-major tile ----
     {
       const uint8_t *src = stage + (size_t)s * tile_bytes;
-      for (int u = tid; u < nunits; u += THREADS) {
+      for (int u = tid; u < ((p.debug & 1) ? 0 : nunits); u += THREADS) {
         uint4 in[R];
 #pragma unroll
         for (int lr = 0; lr < R; ++lr) in[lr] = *reinterpret_cast<const uint4 *>(src + (size_t)lr * rowbytes + (size_t)u * 16);
@@ -282,42 +285,52 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       __syncthreads();
     }
 
-    // ---- phase A: permuted gather + primary quantisation, one 16-group x R rows per thread per step ----
-    for (int g = tid; g < ngroups; g += THREADS) {
-      uint32_t v[16][RP];
-      if constexpr (OWN) {
+    // ---- phase A: permuted gather + primary quantisation; one item = (16-group, block of RT rows) per thread per step ----
+    for (int item = tid; item < ngroups * RB; item += THREADS) {
+      const int g = item / RB, rb = item % RB;
+      uint32_t v[16][RTP];
+      if (p.debug & 2) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) lds_chunk<R>(tile + own_off[i], v[i]);
+        for (int i = 0; i < 16; ++i)
+#pragma unroll
+          for (int w = 0; w < RTP; ++w) v[i][w] = (uint32_t)g * 0x9e3779b9u + i;
+      } else if constexpr (OWN) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + own_off[i] + rb * (2 * RT), v[i]);
       } else {
         uint32_t off[16];
         load_offsets(g, off);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) lds_chunk<R>(tile + off[i], v[i]);
+        for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + off[i] + rb * (2 * RT), v[i]);
       }
       float wf[RMS ? 16 : 1];
       if constexpr (RMS) load_w(g, wf);
       int slot_p, slot_r;
       slots(g, slot_p, slot_r);
-      uint8_t *sfp = sfs + (slot_p >> 2) * (4 * R) + (slot_p & 3);
+      uint8_t *sfp = sfs + (slot_p >> 2) * (4 * R) + (slot_p & 3) + 4 * RT * rb;
       const int dslot = slot_r - slot_p;
       const bool arc = g >= G;
-      uint8_t *qg = qbase + 8 * slot_p;
+      const int drb = TileMap<R>::row(0, rb * RT);  // row(0, rb*RT + lr) = row(0, rb*RT) + row(0, lr) for every TileMap
+      uint8_t *qg = qbase + 8 * slot_p + (uint32_t)drb * khalf;
+      const int mr = mrows - drb;
 #pragma unroll
-      for (int lr = 0; lr < R; ++lr) {
+      for (int lr = 0; lr < RT; ++lr) {
         float x[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           x[i] = (lr & 1) ? bf16hi_to_f32(v[i][lr >> 1]) : bf16lo_to_f32(v[i][lr >> 1]);
           if constexpr (RMS)  // rmsnorm.cu:165-171: bf16((x * w) * rstd), left to right
-            x[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmul_rn(__fmul_rn(x[i], wf[i]), rstd_s[lr])));
+            x[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmul_rn(__fmul_rn(x[i], wf[i]), rstd_s[rb * RT + lr])));
         }
         uint32_t c_lo, c_hi;
         float sc;
-        const uint32_t sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
+        uint32_t sfb;
+        if (p.debug & 4) { sfb = __float_as_uint(x[0]) >> 24; c_lo = __float_as_uint(x[1]); c_hi = __float_as_uint(x[15]); sc = x[2]; }
+        else sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
         sfp[4 * lr] = (uint8_t)sfb;
         if (IS_W && arc) sfp[4 * lr + ((dslot >> 2) * (4 * R) + (dslot & 3))] = (uint8_t)sfb;  // reorder.cu:307-316
         if (!IS_W && arc) {  // hand the residual work of this (group,row) to phase B: values, codes, subtrahend scale
-          uint4 *a = reinterpret_cast<uint4 *>(arcs + ((g - G) * R + lr) * 48);
+          uint4 *a = reinterpret_cast<uint4 *>(arcs + ((g - G) * R + rb * RT + lr) * 48);
           uint32_t xb[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
@@ -327,18 +340,18 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           a[2] = make_uint4(c_lo, c_hi, __float_as_uint(FLAVOUR == 0 ? sf_lut[sfb] : sc), 0u);
         }
         uint8_t *qp = qg + TileMap<R>::row(0, lr) * khalf;
-        if (TileMap<R>::row(0, lr) < mrows) {
+        if (TileMap<R>::row(0, lr) < mr) {
           __stcs(reinterpret_cast<uint2 *>(qp), make_uint2(c_lo, c_hi));
           if (IS_W && arc) __stcs(reinterpret_cast<uint2 *>(qp + 8 * dslot), make_uint2(c_lo, c_hi));
         }
       }
-      if constexpr (OWN) break;  // THREADS >= ngroups: one group per thread, its offsets stay in registers
+      if constexpr (OWN) break;  // THREADS >= items: one item per thread, its offsets stay in registers
     }
 
     // ---- phase B: ARC residuals, one (group, row) item per thread per step, from the stash of phase A ----
     if constexpr (!IS_W) {
       __syncthreads();  // stash complete; also: nobody reads the tile any more (the next transpose may overwrite it)
-      const int nitems = (KE / 16) * R;
+      const int nitems = (p.debug & 8) ? 0 : (KE / 16) * R;
       for (int item = tid; item < nitems; item += THREADS) {
         const int g = G + item / R, lr = item % R;
         const uint4 *a = reinterpret_cast<const uint4 *>(arcs + item * 48);
@@ -370,10 +383,11 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
 constexpr int kSmemPerSm = 227 * 1024;
 
-template <int R, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
 int launch(const QuantParams &p0, int S, cudaStream_t stream) {
   QuantParams p = p0;
-  auto kern = quant_tma_kernel<R, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB>;
+  if (const char *e = getenv("ARCQ_QUANT_DEBUG")) p.debug = atoi(e);
+  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB>;
   const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S).total;
   static int smem_set = 0;  // per instantiation
   if (smem > smem_set) {
@@ -390,23 +404,23 @@ int launch(const QuantParams &p0, int S, cudaStream_t stream) {
   return ARCQ_OK;
 }
 
-template <int R, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS>
+template <int R, int RT, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS>
 int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t st) {
-  if (own) return launch<R, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB>(p, S, st);
-  if (tab32) return launch<R, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB>(p, S, st);
-  return launch<R, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB>(p, S, st);
+  if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB>(p, S, st);
+  if (tab32) return launch<R, RT, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB>(p, S, st);
+  return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB>(p, S, st);
 }
 
-template <int R, int THREADS, int MINB>
+template <int R, int RT, int THREADS, int MINB>
 int launch_kind(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st) {
-  if (rms) return launch_tab<R, THREADS, MINB, 0, false, true>(p, S, tab32, own, st);
-  if (is_w) return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, THREADS, MINB, 1, true, false>(p, S, tab32, own, st)
-                                              : launch_tab<R, THREADS, MINB, 0, true, false>(p, S, tab32, own, st);
-  return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, THREADS, MINB, 1, false, false>(p, S, tab32, own, st)
-                                    : launch_tab<R, THREADS, MINB, 0, false, false>(p, S, tab32, own, st);
+  if (rms) return launch_tab<R, RT, THREADS, MINB, 0, false, true>(p, S, tab32, own, st);
+  if (is_w) return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, true, false>(p, S, tab32, own, st)
+                                              : launch_tab<R, RT, THREADS, MINB, 0, true, false>(p, S, tab32, own, st);
+  return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false>(p, S, tab32, own, st)
+                                    : launch_tab<R, RT, THREADS, MINB, 0, false, false>(p, S, tab32, own, st);
 }
 
-struct Cfg { int R, threads, minb, S; };
+struct Cfg { int R, threads, minb, S, RT; };
 
 }  // namespace
 
@@ -418,18 +432,18 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   const int64_t blocks = ((int64_t)p.M + 127) / 128;
   const int wide = ngroups > 512 ? 1024 : 512;
   // tile height, threads per CTA, CTAs per SM, staging slots -- first candidate that fits and gives every SM a tile
-  const Cfg cands[] = {{4, 256, 2, 2}, {4, 512, 1, 2}, {2, 256, 2, 2}, {2, wide, 1, 2}, {2, wide, 1, 1},
-                       {1, wide, 1, 2}, {1, wide, 1, 1}};
-  Cfg c{0, 0, 0, 0};
+  const Cfg cands[] = {{4, 256, 2, 2, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
+                       {1, wide, 1, 2, 1}, {1, wide, 1, 1, 1}};
+  Cfg c{0, 0, 0, 0, 0};
   bool tab32 = false, own = false;
   if (const char *e = getenv("ARCQ_QUANT_TMA")) {  // experiment knob: "R,threads,S" (threads 256 = two CTAs per SM)
-    int r = 0, th = 0, s = 0;
-    if (sscanf(e, "%d,%d,%d", &r, &th, &s) == 3) c = Cfg{r, th, th == 256 ? 2 : 1, s};
+    int r = 0, th = 0, s = 0, rt = 0, mb = 0;  // "R,threads,S[,RT,CTAs/SM]"
+    const int nf = sscanf(e, "%d,%d,%d,%d,%d", &r, &th, &s, &rt, &mb);
+    if (nf >= 3) c = Cfg{r, th, nf >= 5 ? mb : (th == 256 ? 2 : 1), s, nf >= 4 ? rt : r};
   }
   if (c.R == 0) {
     for (const Cfg &k : cands) {
       if (rms && k.threads < 32 * k.R) continue;
-      const bool o = ngroups <= k.threads;
       const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
       if (need * k.minb > kSmemPerSm) continue;
       if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;
@@ -438,13 +452,15 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     }
     if (c.R == 0) return ARCQ_ENOSUP;
   }
-  own = ngroups <= c.threads;
+  own = ngroups * (c.R / c.RT) <= c.threads;
   tab32 = !own && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
   if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
-#define ARCQ_T(RR, TH, MB) \
-  if (c.R == RR && c.threads == TH && c.minb == MB) return launch_kind<RR, TH, MB>(p, flavour, is_w, rms, c.S, tab32, own, stream);
-  ARCQ_T(8, 512, 1) ARCQ_T(4, 256, 2) ARCQ_T(4, 512, 1) ARCQ_T(2, 256, 2) ARCQ_T(2, 512, 1) ARCQ_T(2, 1024, 1)
-  ARCQ_T(1, 512, 1) ARCQ_T(1, 1024, 1)
+#define ARCQ_T(RR, RTT, TH, MB) \
+  if (c.R == RR && c.RT == RTT && c.threads == TH && c.minb == MB) \
+    return launch_kind<RR, RTT, TH, MB>(p, flavour, is_w, rms, c.S, tab32, own, stream);
+  ARCQ_T(8, 8, 512, 1) ARCQ_T(4, 4, 256, 2) ARCQ_T(4, 4, 512, 1) ARCQ_T(2, 2, 256, 2) ARCQ_T(2, 2, 512, 1) ARCQ_T(2, 2, 1024, 1)
+  ARCQ_T(1, 1, 512, 1) ARCQ_T(1, 1, 1024, 1)
+  ARCQ_T(4, 2, 512, 2) ARCQ_T(8, 4, 1024, 1) ARCQ_T(8, 4, 512, 1) ARCQ_T(4, 2, 1024, 1) ARCQ_T(2, 1, 1024, 1)  // finer items, more warps
 #undef ARCQ_T
   return ARCQ_ENOSUP;
 }

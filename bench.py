@@ -46,6 +46,16 @@ def gemm_bytes(M, N, K):
     return 0.5625 * K * (M + N) + 2.0 * M * N
 
 
+def load_ncu_summary():
+    """Per-launch DRAM traffic / tensor-pipe activity of the dominant kernels from the committed `ncu --set full`
+    capture of this same step (profiles/ncu_summary.json, written from the .ncu-rep by scripts/ncu_summary.py)."""
+    p = os.path.join(ROOT, "profiles", "ncu_summary.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return json.load(f)
+    return {}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -69,7 +79,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
@@ -211,16 +221,47 @@ class Layer:
                     self.dist.all_reduce(y)
 
     def step_e2e(self):
-        """Same step through the public API with host buffers: H2D of every activation, D2H of every result."""
-        ag = self.agemm
+        """Same step through the public API with HOST buffers: H2D of every activation (pinned -> device) and D2H of
+        every result inside the step.  Copies run on their own streams and are ordered against the kernels with events,
+        so PCIe traffic of one linear overlaps the kernels of another; nothing is skipped or cached."""
+        torch, ag = self.torch, self.agemm
+        cur = torch.cuda.current_stream()
+        if not hasattr(self, "_h2d"):
+            self._h2d, self._d2h = torch.cuda.Stream(), torch.cuda.Stream()
+            for it in self.items:
+                it["x_in"] = torch.empty_like(it["x"])
+                it["ev_in"], it["ev_read"] = torch.cuda.Event(), torch.cuda.Event()
+                it["ev_y"] = [torch.cuda.Event() for _ in it["y"]]
+                it["ev_out"] = [torch.cuda.Event() for _ in it["y"]]
+                it["ev_read"].record(cur)
+                for e in it["ev_out"]:
+                    e.record(self._d2h)
+        with torch.cuda.stream(self._h2d):
+            for it in self.items:
+                self._h2d.wait_event(it["ev_read"])  # the previous step's quantise has consumed x_in
+                it["x_in"].copy_(it["x_host"], non_blocking=True)
+                it["ev_in"].record(self._h2d)
         for it in self.items:
-            x = it["x_host"].to(it["x"].device, non_blocking=True)
-            qx, sfx = ag.reorder_quantize_x(x, it["idx"], it["KE"])
-            for (N, qw, sfw, sw), y, yh in zip(it["w"], it["y"], it["y_host"]):
+            cur.wait_event(it["ev_in"])
+            qx, sfx = ag.reorder_quantize_x(it["x_in"], it["idx"], it["KE"])
+            it["ev_read"].record(cur)
+            for j, ((N, qw, sfw, sw), y, yh) in enumerate(zip(it["w"], it["y"], it["y_host"])):
+                cur.wait_event(it["ev_out"][j])  # the previous step's D2H of this buffer is done
                 ag.matmul(qx, qw, sfx, sfw, sw, out=y)
                 if it["reduce"]:
                     self.dist.all_reduce(y)
-                yh.copy_(y, non_blocking=True)
+                it["ev_y"][j].record(cur)
+                with torch.cuda.stream(self._d2h):
+                    self._d2h.wait_event(it["ev_y"][j])
+                    yh.copy_(y, non_blocking=True)
+                    it["ev_out"][j].record(self._d2h)
+
+    def e2e_join(self):
+        """Make the current stream wait for every outstanding copy (closes the timed region of step_e2e)."""
+        cur = self.torch.cuda.current_stream()
+        if hasattr(self, "_d2h"):
+            cur.wait_stream(self._d2h)
+            cur.wait_stream(self._h2d)
 
     def flops(self):
         return sum(2.0 * self.M * N * (it["KQ"] + it["KE"]) for it in self.items for (N, _, _, _) in it["w"])
@@ -288,10 +329,12 @@ def run_native(args):
     # ---- e2e: host activations in, results out, inside the timed region ----
     for _ in range(2):
         layer.step_e2e()
+    layer.e2e_join()
     barrier()
     e0.record()
     for _ in range(args.e2e_steps):
         layer.step_e2e()
+    layer.e2e_join()
     e1.record()
     barrier()
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
@@ -327,6 +370,7 @@ def run_native(args):
             fl = 2.0 * M * N * (KQ + KE)
             kernels.append({"kernel": "gemm", "N": N, "K": KQ + KE, "us": 1e3 * avg, "calls_per_step": calls_per_step,
                             "TFLOPs": fl / (avg * 1e-3) / 1e12})
+    ncu = load_ncu_summary() if (M == 8192 and world == 1) else {}
     gemms = [k for k in kernels if k["kernel"] == "gemm"]
     dom = max(gemms, key=lambda k: k["us"] * k["calls_per_step"])
     nvfp4_peak = 4.0 * peaks["bf16_tflops"]
@@ -334,12 +378,17 @@ def run_native(args):
                 "achieved": dom["TFLOPs"], "peak": nvfp4_peak, "unit": "TFLOP/s", "frac": dom["TFLOPs"] / nvfp4_peak,
                 "peak_basis": "4 x %s cuBLAS bf16 burst (%.1f TF/s) from MEASURED_PEAKS.json; nominal dense NVFP4 is 9000"
                               % (peaks["source"], peaks["bf16_tflops"]),
-                "frac_of_nominal_9000": dom["TFLOPs"] / 9000.0, "traffic": None,
+                "frac_of_nominal_9000": dom["TFLOPs"] / 9000.0,
+                "traffic": ncu.get("gemm_N%d_K%d" % (dom["N"], dom["K"]), {}).get("dram_bytes"),
+                "ncu_tensor_pipe_active_pct": ncu.get("gemm_N%d_K%d" % (dom["N"], dom["K"]), {}).get("tensor_pipe_active_pct"),
+                "algorithmic_bytes": gemm_bytes(M, dom["N"], dom["K"]),
                 "share_of_step": dom["us"] * dom["calls_per_step"] / (1e3 * total_ms)}
     qk = max([k for k in kernels if k["kernel"] == "quant"], key=lambda k: k["us"])
     roofline_quant = {"bound": "hbm", "kernel": "quant_kernel KQ=%d KE=%d M=%d" % (qk["KQ"], qk["KE"], M),
                       "achieved": qk["GBps"], "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": qk["frac_hbm"],
-                      "peak_basis": "%s copy bandwidth" % peaks["source"], "traffic": None}
+                      "peak_basis": "%s copy bandwidth" % peaks["source"],
+                      "traffic": ncu.get("quant_KQ%d" % qk["KQ"], {}).get("dram_bytes"),
+                      "algorithmic_bytes": quant_bytes(M, qk["KQ"], qk["KE"])}
 
     # ---- CPU baseline on this box's host cores (bounded sample) ----
     cpu = None
@@ -384,13 +433,13 @@ def run_native(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--tokens", type=int, default=8192, help="M: rows (tokens) per GPU per step")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--parallelism", default="tp", choices=["tp", "replicas"],
                     help="N>1: tensor-parallel shards of one layer (default, north star) or independent token replicas")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-tokens", type=int, default=512)
     ap.add_argument("--cpu-reps", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
