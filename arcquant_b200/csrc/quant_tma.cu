@@ -430,7 +430,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   if (sms <= 0) return ARCQ_ECUDA;
   const int ngroups = p.KQ / 16;
   const int64_t blocks = ((int64_t)p.M + 127) / 128;
-  const int wide = ngroups > 512 ? 1024 : 512;
+  const int wide = 512;  // 1024 threads (64 registers) measured slower than 512 on KQ=14336 (profiles/r1_quant_v3.log)
   // tile height, threads per CTA, CTAs per SM, staging slots -- first candidate that fits and gives every SM a tile
   const Cfg cands[] = {{4, 256, 2, 2, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
                        {1, wide, 1, 2, 1}, {1, wide, 1, 1, 1}};

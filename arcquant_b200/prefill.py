@@ -1,0 +1,165 @@
+"""Prefill harness: a Llama/Qwen-shaped decoder stack whose linears run on the NVFP4+ARC hot path.
+
+Mirrors how the reference's speed model drives ``agemm`` (benchmarks/modeling_arc.py: ``LlamaRMSNorm.forward`` :220-227
+-> ``rmsnorm_quantize_x``; ``QLlamaAttention.forward`` :156-209 -> q/k/v ``matmul`` on the shared quantised
+activation, attention, ``reorder_quantize_x`` + o_proj; ``QLlamaMLP.forward`` :108-110 -> gate/up ``matmul``,
+SiLU*up, ``reorder_quantize_x`` + down_proj; ``LlamaDecoderLayer.forward`` :268-300 residual adds).  Differences:
+random-init weights (no checkpoints here), attention through torch SDPA instead of flashinfer (attention is not on
+the hot path), per-tensor scales kept on the device (no host sync), and optional tensor parallelism
+(arcquant_b200/tp.py: q/k/v/gate/up column-parallel, o/down row-parallel + all-reduce).
+
+Only the linears and the quantisers are this repo's kernels; everything else is plain torch glue.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from . import tp
+
+MODELS = {
+    # name: hidden, intermediate, heads, layers, qkv bias  (speed-model shapes: MHA, benchmarks/modeling_arc.py:139-154)
+    "qwen2.5-7b": (3584, 18944, 28, 28, True),
+    "llama-3-8b": (4096, 14336, 32, 32, False),
+    "qwen2.5-32b": (5120, 27648, 40, 64, True),
+    "llama-3-70b": (8192, 28672, 64, 80, False),
+    "tiny": (2048, 4096, 16, 2, True),
+}
+
+
+@dataclass
+class PrefillConfig:
+    hidden: int
+    intermediate: int
+    heads: int
+    layers: int
+    qkv_bias: bool
+    ke_hidden: int = 256       # select_num of the hidden-size inputs (multiple of 64, utilize.py:475)
+    ke_intermediate: int = 512
+    eps: float = 1e-6
+
+    @staticmethod
+    def named(name: str, layers: int | None = None) -> "PrefillConfig":
+        h, i, nh, nl, b = MODELS[name]
+        return PrefillConfig(h, i, nh, layers if layers is not None else nl, b)
+
+
+def _rand_weight(n, k, dev, gen):
+    return (torch.randn(n, k, device=dev, generator=gen) * 0.02).to(torch.bfloat16)
+
+
+def _rand_index(k, dev, gen):
+    return torch.randperm(k, device=dev, generator=gen).to(torch.int16)
+
+
+def _rope(q, k):
+    """LLaMA rotary embedding on [B, H, S, D] (reference: flashinfer pos_encoding_mode="ROPE_LLAMA")."""
+    b, h, s, d = q.shape
+    inv = 1.0 / (10000 ** (torch.arange(0, d, 2, device=q.device, dtype=torch.float32) / d))
+    f = torch.outer(torch.arange(s, device=q.device, dtype=torch.float32), inv)
+    cos, sin = torch.cat((f, f), -1).cos().to(q.dtype), torch.cat((f, f), -1).sin().to(q.dtype)
+
+    def rot(x):
+        return torch.cat((-x[..., d // 2:], x[..., : d // 2]), -1)
+
+    return q * cos + rot(q) * sin, k * cos + rot(k) * sin
+
+
+class ArcDecoderLayer(torch.nn.Module):
+    def __init__(self, cfg: PrefillConfig, dev, gen, world=1, rank=0, group=None, keep_ref=False):
+        super().__init__()
+        from . import agemm
+        self.ref = {} if keep_ref else None  # bf16 weights / biases kept only for the parity test
+        self.agemm, self.cfg, self.world, self.rank, self.group = agemm, cfg, world, rank, group
+        H, I = cfg.hidden, cfg.intermediate
+        if cfg.heads % world or I % (64 * world):
+            raise ValueError("heads=%d / intermediate=%d do not shard over %d ranks" % (cfg.heads, I, world))
+        self.local_heads = cfg.heads // world
+        self.head_dim = H // cfg.heads
+        self.idx_h1, self.idx_h2 = _rand_index(H, dev, gen), _rand_index(H, dev, gen)  # inputs of qkv and of gate/up
+        idx_o, idx_d = _rand_index(H, dev, gen), _rand_index(I, dev, gen)
+        self.norm1 = torch.ones(H, dtype=torch.bfloat16, device=dev)
+        self.norm2 = torch.ones(H, dtype=torch.bfloat16, device=dev)
+
+        def bias(n):
+            return (torch.randn(n, device=dev, generator=gen) * 0.02).to(torch.bfloat16) if cfg.qkv_bias else None
+
+        def weight(name, n, k, b=None):
+            w = _rand_weight(n, k, dev, gen)
+            if self.ref is not None:
+                self.ref[name] = (w, b)
+            return w
+
+        def col(name, n, k, idx, ke, b=None):
+            return tp.ColumnParallelQLinear(weight(name, n, k, b), idx, ke, world, rank, b)
+
+        self.q = col("q", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
+        self.k = col("k", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
+        self.v = col("v", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
+        self.gate = col("gate", I, H, self.idx_h2, cfg.ke_hidden)
+        self.up = col("up", I, H, self.idx_h2, cfg.ke_hidden)
+        self.o = tp.RowParallelQLinear(weight("o", H, H), idx_o, cfg.ke_hidden, world, rank, group=group)
+        self.down = tp.RowParallelQLinear(weight("down", H, I), idx_d, cfg.ke_intermediate, world, rank, group=group)
+
+    def _norm_linears(self, x2d, w, idx, ke, layers):
+        """One fused rmsnorm+quantise launch feeding several column-parallel GEMMs (modeling_arc.py:220-227)."""
+        qx, sfx = self.agemm.rmsnorm_quantize_x(x2d, w, self.cfg.eps, idx, ke)
+        return [l.forward_quantized(qx, sfx, 1.0) for l in layers]
+
+    @torch.no_grad()
+    def forward(self, h):
+        B, S, H = h.shape
+        x2d = h.reshape(B * S, H)
+        q, k, v = self._norm_linears(x2d, self.norm1, self.idx_h1, self.cfg.ke_hidden, (self.q, self.k, self.v))
+        shp = (B, S, self.local_heads, self.head_dim)
+        q, k, v = (t.view(shp).transpose(1, 2) for t in (q, k, v))
+        q, k = _rope(q, k)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B * S, -1).contiguous()
+        h = h + self.o(a).view(B, S, H)                       # quantise (local permutation + ARC) -> GEMM -> all-reduce
+        x2d = h.reshape(B * S, H)
+        g, u = self._norm_linears(x2d, self.norm2, self.idx_h2, self.cfg.ke_hidden, (self.gate, self.up))
+        m = (F.silu(g) * u).contiguous()
+        return h + self.down(m).view(B, S, H)
+
+
+def reference_layer_forward(layer: "ArcDecoderLayer", h: torch.Tensor) -> torch.Tensor:
+    """The same decoder layer in plain fp32 torch with the UNQUANTISED weights (needs keep_ref=True): test oracle."""
+    c, r = layer.cfg, layer.ref
+    lin = lambda name, x: F.linear(x, r[name][0].float(), None if r[name][1] is None else r[name][1].float())
+
+    def rms(x, w):
+        return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + c.eps) * w.float()
+
+    B, S, H = h.shape
+    h = h.float()
+    x = rms(h, layer.norm1)
+    shp = (B, S, c.heads, H // c.heads)
+    q, k, v = (lin(n, x).view(shp).transpose(1, 2) for n in ("q", "k", "v"))
+    q, k = _rope(q, k)
+    a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, S, H)
+    h = h + lin("o", a)
+    x = rms(h, layer.norm2)
+    return h + lin("down", F.silu(lin("gate", x)) * lin("up", x))
+
+
+class ArcPrefillModel(torch.nn.Module):
+    def __init__(self, cfg: PrefillConfig, device, seed=0, world=1, rank=0, group=None, keep_ref=False):
+        super().__init__()
+        gen = torch.Generator(device=device).manual_seed(seed)  # same seed on every rank: shards of the same weights
+        self.cfg = cfg
+        self.layers = torch.nn.ModuleList([ArcDecoderLayer(cfg, device, gen, world, rank, group, keep_ref) for _ in range(cfg.layers)])
+
+    @torch.no_grad()
+    def forward(self, h):
+        for layer in self.layers:
+            h = layer(h)
+        return h
+
+    def linear_flops(self, tokens: int) -> float:
+        c = self.cfg
+        per = 2.0 * tokens * (4 * c.hidden * (c.hidden + c.ke_hidden) + 2 * c.intermediate * (c.hidden + c.ke_hidden)
+                              + c.hidden * (c.intermediate + c.ke_intermediate))
+        return per * c.layers
