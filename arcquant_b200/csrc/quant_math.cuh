@@ -26,6 +26,20 @@ static __device__ __forceinline__ void e2m1x8_to_f16x2(uint32_t w, uint32_t (&d)
       : "r"(w));
 }
 
+// 4 floats -> 4 e2m1 nibbles (element 0 in the low nibble), RNE, saturating; same conversion as f32x8_to_e2m1
+static __device__ __forceinline__ uint32_t f32x4_to_e2m1(float a0, float a1, float a2, float a3) {
+  uint16_t r;
+  asm("{\n\t"
+      ".reg .b8 b0, b1;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b0, %2, %1;\n\t"
+      "cvt.rn.satfinite.e2m1x2.f32 b1, %4, %3;\n\t"
+      "mov.b16 %0, {b0, b1};\n\t"
+      "}"
+      : "=h"(r)
+      : "f"(a0), "f"(a1), "f"(a2), "f"(a3));
+  return (uint32_t)r;
+}
+
 // primary quantisation of 16 values (reorder.cu:127-165): returns the E4M3 byte; s = unrounded clamped scale
 static __device__ __forceinline__ uint32_t quant16(const float (&x)[16], const float *rcp_lut, uint32_t &c_lo, uint32_t &c_hi,
                                             float &s) {

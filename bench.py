@@ -165,27 +165,37 @@ ROW_PARALLEL = ("o", "down")  # K-split + all-reduce; the others are N-split (SU
 class Layer:
     """Device-resident state of one Llama-3-8B layer's linears: quantised weights + activation buffers.
     world > 1: this rank's tensor-parallel shard (arcquant_b200/tp.py): qkv and gate/up split N, o and down split K by
-    channel ownership with their ARC columns and are followed by an all-reduce of the bf16 partials."""
+    channel ownership with their ARC columns.  Exchange steps:
+      mode "tp"    (default) sequence-parallel edges: the row-parallel partials are REDUCE-SCATTERED over tokens, and the
+                   column-parallel inputs are quantised on the rank's own M/world tokens and ALL-GATHERED as 4.5-bit
+                   codes + scales (0.5625 B/element on the wire instead of 2 B of bf16);
+      mode "tp-ar" plain all-reduce of the bf16 partials after o and down (activations replicated)."""
 
-    def __init__(self, torch, agemm, M, dev, seed=0, world=1, rank=0):
+    def __init__(self, torch, agemm, M, dev, seed=0, world=1, rank=0, sp=True):
         from tests._util import make_acts
         from arcquant_b200 import tp
         self.torch, self.agemm, self.M, self.world = torch, agemm, M, world
+        self.sp = sp and world > 1
+        if self.sp and M % (128 * world):
+            raise SystemExit("bench.py: tokens must be a multiple of 128 * world for the sequence-parallel edges")
         self.items = []
         g = torch.Generator().manual_seed(seed)
         for name, KQ, KE, Ns in LLAMA3_8B_LAYER:
             xs, idx = make_acts(min(M, 256), KQ, KE, seed=seed + KQ)  # distribution A, pre-scaled
             row = name in ROW_PARALLEL and world > 1
+            gather = self.sp and not row
             if row:
                 lo, hi = tp.split_rows(KQ, world, rank, 64)
                 idx, KE = tp.shard_reorder_index(idx, KE, world, rank)
                 xs, KQ = xs[:, lo:hi].contiguous(), hi - lo
             elif world > 1:
                 Ns = [n // world for n in Ns]
-            reps = (M + xs.shape[0] - 1) // xs.shape[0]
-            x_host = xs.repeat(reps, 1)[:M].contiguous()
+            Mx = M // world if gather else M          # rows this rank quantises
+            My = M // world if (row and self.sp) else M  # rows of the result this rank keeps
+            reps = (Mx + xs.shape[0] - 1) // xs.shape[0]
+            x_host = xs.repeat(reps, 1)[:Mx].contiguous()
             # de-correlate repeated blocks cheaply: flip signs per row block
-            sign = (torch.randint(0, 2, (M, 1), generator=g) * 2 - 1).to(torch.bfloat16)
+            sign = (torch.randint(0, 2, (Mx, 1), generator=g) * 2 - 1).to(torch.bfloat16)
             x_host = (x_host * sign).contiguous().pin_memory()
             idx_d = idx.to(dev)
             ws = []
@@ -194,48 +204,68 @@ class Layer:
                 sw = w.max().float() / (448.0 * 6.0)
                 qw, sfw = agemm.reorder_quantize_w((w / sw).to(torch.bfloat16).to(dev), idx_d, KE)
                 ws.append((N, qw, sfw, float(sw)))
-            self.items.append({"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host, "reduce": row,
-                               "x": x_host.to(dev), "w": ws,
-                               "y": [torch.empty((M, N), dtype=torch.bfloat16, device=dev) for N in Ns],
-                               "y_host": [torch.empty((M, N), dtype=torch.bfloat16).pin_memory() for N in Ns]})
+            K = KQ + KE
+            it = {"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host, "reduce": row, "gather": gather,
+                  "x": x_host.to(dev), "w": ws,
+                  "y": [torch.empty((M, N), dtype=torch.bfloat16, device=dev) for N in Ns],
+                  "y_host": [torch.empty((My, N), dtype=torch.bfloat16).pin_memory() for N in Ns]}
+            if gather:
+                it["qx_full"] = torch.empty((M, K // 2), dtype=torch.uint8, device=dev)
+                it["sfx_full"] = torch.zeros((agemm.sf_bytes(M, K),), dtype=torch.uint8, device=dev)
+                it["sf_valid"] = (M * K // 16, Mx * K // 16)
+            if row and self.sp:
+                it["y_rs"] = [torch.empty((My, N), dtype=torch.bfloat16, device=dev) for N in Ns]
+            self.items.append(it)
         torch.cuda.synchronize()
+
+    def _item(self, it, x, events=None):
+        """One quantise launch + its GEMMs (+ the exchange steps of the tensor-parallel modes); returns the results."""
+        ag, torch = self.agemm, self.torch
+        if events is not None:
+            e0 = torch.cuda.Event(enable_timing=True); e0.record()
+        qx, sfx = ag.reorder_quantize_x(x, it["idx"], it["KE"])
+        if events is not None:
+            e1 = torch.cuda.Event(enable_timing=True); e1.record()
+            events.append(("quant", it["KQ"], it["KE"], 0, x.shape[0], e0, e1))
+        if it["gather"]:  # every rank quantised its own tokens: gather the codes and the 128-row scale blocks
+            full, mine = it["sf_valid"]
+            self.dist.all_gather_into_tensor(it["qx_full"], qx)
+            self.dist.all_gather_into_tensor(it["sfx_full"][:full], sfx[:mine])
+            qx, sfx = it["qx_full"], it["sfx_full"]
+        outs = []
+        for j, ((N, qw, sfw, sw), y) in enumerate(zip(it["w"], it["y"])):
+            if events is not None:
+                e0 = torch.cuda.Event(enable_timing=True); e0.record()
+            ag.matmul(qx, qw, sfx, sfw, sw, out=y)
+            if events is not None:
+                e1 = torch.cuda.Event(enable_timing=True); e1.record()
+                events.append(("gemm", it["KQ"], it["KE"], N, self.M, e0, e1))
+            if it["reduce"] and self.sp:
+                self.dist.reduce_scatter_tensor(it["y_rs"][j], y)
+                y = it["y_rs"][j]
+            elif it["reduce"]:
+                self.dist.all_reduce(y)
+            outs.append(y)
+        return outs
 
     def step(self, events=None):
         """4 quantise + 7 GEMM launches, inputs resident in HBM."""
-        ag = self.agemm
         for it in self.items:
-            if events is not None:
-                e0 = self.torch.cuda.Event(enable_timing=True); e0.record()
-            qx, sfx = ag.reorder_quantize_x(it["x"], it["idx"], it["KE"])
-            if events is not None:
-                e1 = self.torch.cuda.Event(enable_timing=True); e1.record()
-                events.append(("quant", it["KQ"], it["KE"], 0, e0, e1))
-            for (N, qw, sfw, sw), y in zip(it["w"], it["y"]):
-                if events is not None:
-                    e0 = self.torch.cuda.Event(enable_timing=True); e0.record()
-                ag.matmul(qx, qw, sfx, sfw, sw, out=y)
-                if events is not None:
-                    e1 = self.torch.cuda.Event(enable_timing=True); e1.record()
-                    events.append(("gemm", it["KQ"], it["KE"], N, e0, e1))
-                if it["reduce"]:
-                    self.dist.all_reduce(y)
+            self._item(it, it["x"], events)
 
     def step_e2e(self):
         """Same step through the public API with HOST buffers: H2D of every activation (pinned -> device) and D2H of
         every result inside the step.  Copies run on their own streams and are ordered against the kernels with events,
         so PCIe traffic of one linear overlaps the kernels of another; nothing is skipped or cached."""
-        torch, ag = self.torch, self.agemm
+        torch = self.torch
         cur = torch.cuda.current_stream()
         if not hasattr(self, "_h2d"):
             self._h2d, self._d2h = torch.cuda.Stream(), torch.cuda.Stream()
             for it in self.items:
                 it["x_in"] = torch.empty_like(it["x"])
-                it["ev_in"], it["ev_read"] = torch.cuda.Event(), torch.cuda.Event()
-                it["ev_y"] = [torch.cuda.Event() for _ in it["y"]]
-                it["ev_out"] = [torch.cuda.Event() for _ in it["y"]]
+                it["ev_in"], it["ev_read"], it["ev_y"], it["ev_out"] = (torch.cuda.Event() for _ in range(4))
                 it["ev_read"].record(cur)
-                for e in it["ev_out"]:
-                    e.record(self._d2h)
+                it["ev_out"].record(self._d2h)
         with torch.cuda.stream(self._h2d):
             for it in self.items:
                 self._h2d.wait_event(it["ev_read"])  # the previous step's quantise has consumed x_in
@@ -243,18 +273,15 @@ class Layer:
                 it["ev_in"].record(self._h2d)
         for it in self.items:
             cur.wait_event(it["ev_in"])
-            qx, sfx = ag.reorder_quantize_x(it["x_in"], it["idx"], it["KE"])
+            cur.wait_event(it["ev_out"])  # the previous step's D2H of this item's result buffers is done
+            outs = self._item(it, it["x_in"])
             it["ev_read"].record(cur)
-            for j, ((N, qw, sfw, sw), y, yh) in enumerate(zip(it["w"], it["y"], it["y_host"])):
-                cur.wait_event(it["ev_out"][j])  # the previous step's D2H of this buffer is done
-                ag.matmul(qx, qw, sfx, sfw, sw, out=y)
-                if it["reduce"]:
-                    self.dist.all_reduce(y)
-                it["ev_y"][j].record(cur)
-                with torch.cuda.stream(self._d2h):
-                    self._d2h.wait_event(it["ev_y"][j])
+            it["ev_y"].record(cur)
+            with torch.cuda.stream(self._d2h):
+                self._d2h.wait_event(it["ev_y"])
+                for y, yh in zip(outs, it["y_host"]):
                     yh.copy_(y, non_blocking=True)
-                    it["ev_out"][j].record(self._d2h)
+                it["ev_out"].record(self._d2h)
 
     def e2e_join(self):
         """Make the current stream wait for every outstanding copy (closes the timed region of step_e2e)."""
@@ -266,8 +293,11 @@ class Layer:
     def flops(self):
         return sum(2.0 * self.M * N * (it["KQ"] + it["KE"]) for it in self.items for (N, _, _, _) in it["w"])
 
-    def allreduce_bytes(self):
-        return sum(y.numel() * 2 for it in self.items if it["reduce"] for y in it["y"])
+    def exchange_bytes(self):
+        """Bytes this rank hands to NCCL per step (collective inputs)."""
+        b = sum(y.numel() * 2 for it in self.items if it["reduce"] for y in it["y"])
+        b += sum(it["qx_full"].numel() + it["sf_valid"][0] for it in self.items if it["gather"]) // max(self.world, 1)
+        return b
 
     def e2e_bytes(self):
         h2d = sum(it["x_host"].numel() * 2 for it in self.items)
@@ -286,12 +316,15 @@ def run_native(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version there)
         dist.init_process_group("nccl", device_id=dev)
     from arcquant_b200 import agemm
     peaks = load_peaks()
     M = args.tokens
-    tp_mode = world > 1 and args.parallelism == "tp"
-    layer = Layer(torch, agemm, M, dev, world=world if tp_mode else 1, rank=rank if tp_mode else 0)
+    tp_mode = world > 1 and args.parallelism in ("tp", "tp-ar")
+    layer = Layer(torch, agemm, M, dev, world=world if tp_mode else 1, rank=rank if tp_mode else 0,
+                  sp=args.parallelism == "tp")
     layer.dist = dist
 
     def barrier():
@@ -354,8 +387,10 @@ def run_native(args):
             dist.destroy_process_group()
         return
     per = {}
-    for kind, KQ, KE, N, a, b in events:
+    rows_of = {}
+    for kind, KQ, KE, N, rows, a, b in events:
         per.setdefault((kind, KQ, KE, N), []).append(a.elapsed_time(b))
+        rows_of[(kind, KQ, KE, N)] = rows
     kernels = []
     total_ms = 0.0
     for (kind, KQ, KE, N), v in sorted(per.items()):
@@ -363,7 +398,7 @@ def run_native(args):
         calls_per_step = len(v) / args.steps
         total_ms += avg * calls_per_step
         if kind == "quant":
-            by = quant_bytes(M, KQ, KE)
+            by = quant_bytes(rows_of[(kind, KQ, KE, N)], KQ, KE)
             kernels.append({"kernel": "quant", "KQ": KQ, "KE": KE, "us": 1e3 * avg, "calls_per_step": calls_per_step,
                             "GBps": by / (avg * 1e-3) / 1e9, "frac_hbm": by / (avg * 1e-3) / 1e9 / peaks["hbm_gbs"]})
         else:
@@ -415,8 +450,10 @@ def run_native(args):
                                "+ 7 x block-scaled GEMM per step", "tokens_per_gpu": M, "tokens_global": M if tp_mode else M * world,
                    "select_num": {n: ke for n, _, ke, _ in LLAMA3_8B_LAYER},
                    "l2": "inputs larger than L2 (per-step working set > 1 GB vs 126 MB L2); no flush needed",
-                   "parallelism": ("tp%d: qkv/gate/up column-parallel, o/down row-parallel (ARC columns with their shard) + NCCL "
-                                   "all-reduce of %d bf16 bytes per step" % (world, layer.allreduce_bytes())) if tp_mode
+                   "parallelism": ("tp%d: qkv/gate/up column-parallel, o/down row-parallel (ARC columns with their shard); %s; "
+                                   "%d bytes per rank per step into NCCL" % (
+                                       world, "reduce-scatter of bf16 partials + all-gather of NVFP4 codes/scales (sequence-parallel edges)"
+                                       if layer.sp else "all-reduce of bf16 partials", layer.exchange_bytes())) if tp_mode
                    else ("replicas (token-parallel), no collective" if world > 1 else "single GPU")},
         "tokens_per_s_linear_path": (M if tp_mode else world * M) * args.steps / (ms_max * 1e-3),
         "e2e": {"value": e2e_val, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -437,8 +474,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--tokens", type=int, default=8192, help="M: rows (tokens) per GPU per step")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--parallelism", default="tp", choices=["tp", "replicas"],
-                    help="N>1: tensor-parallel shards of one layer (default, north star) or independent token replicas")
+    ap.add_argument("--parallelism", default="tp", choices=["tp", "tp-ar", "replicas"],
+                    help="N>1: tensor-parallel shards of one layer with reduce-scatter + quantised all-gather (default), "
+                         "with plain all-reduce (tp-ar), or independent token replicas")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-tokens", type=int, default=512)
     ap.add_argument("--cpu-reps", type=int, default=8)

@@ -105,3 +105,22 @@ def test_row_and_column_parallel_world2_gloo(tmp_path):
     for got in (d["y"], d["ycol"]):
         rel = np.linalg.norm(got - ref) / np.linalg.norm(ref)
         assert rel < 0.12, rel
+
+
+def test_row_slices_quantise_independently():
+    """Sequence-parallel edge of bench.py's TP mode: every rank quantises its own M/world tokens and the codes + the
+    128-row scale blocks are all-gathered.  That is exact because rows are independent and scale blocks are 128-row
+    aligned: concatenating per-slice outputs reproduces quantising the whole matrix byte for byte."""
+    O = oracle.lib()
+    M, KQ, KE, world = 512, 1024, 128, 4
+    x, idx = make_acts(M, KQ, KE, seed=9)
+    K = KQ + KE
+    q_full, sf_full = O.quantize_x(bits(x), idx.numpy(), KE, 0)
+    qs, sfs = [], []
+    for r in range(world):
+        lo, hi = tp.split_rows(M, world, r, 128)
+        q, sf = O.quantize_x(bits(x[lo:hi]), idx.numpy(), KE, 0)
+        qs.append(q)
+        sfs.append(sf[: (hi - lo) * K // 16])
+    assert np.array_equal(np.concatenate(qs), q_full)
+    assert np.array_equal(np.concatenate(sfs), sf_full[: M * K // 16])
