@@ -55,6 +55,26 @@ def launch_count() -> int:
     return int(_lib.load().arcq_launch_count())
 
 
+class _on:
+    """`with torch.cuda.device(dev)` only when dev is not already current (the context manager costs microseconds)."""
+    __slots__ = ("ctx",)
+
+    def __init__(self, dev):
+        self.ctx = None if dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        if self.ctx is not None:
+            self.ctx.__exit__(*a)
+
+
+def _sf_bytes(rows: int, K: int) -> int:  # == arcq_sf_bytes, without the ctypes round trip
+    return (rows // 128 + 1) * 128 * K // 16
+
+
 def _quant(fn_name, X, reorder_index, KE, flavour):
     L = _lib.load()
     _need(X, "X", torch.bfloat16, 2)
@@ -64,12 +84,13 @@ def _quant(fn_name, X, reorder_index, KE, flavour):
         raise RuntimeError("reorder_index must hold %d int16 entries on %s" % (KQ, X.device))
     KE = int(KE)
     K = KQ + KE
-    with torch.cuda.device(X.device):
+    with _on(X.device):
         q = torch.empty((M, K // 2), dtype=torch.uint8, device=X.device)
-        sf = torch.empty((sf_bytes(M, K),), dtype=torch.uint8, device=X.device)
+        sf = torch.empty((_sf_bytes(M, K),), dtype=torch.uint8, device=X.device)
         rc = getattr(L, fn_name)(X.data_ptr(), M, KQ, reorder_index.data_ptr(), KE, flavour,
                                  q.data_ptr(), sf.data_ptr(), _stream(X))
-    _lib.check(rc, fn_name)
+    if rc:
+        _lib.check(rc, fn_name)
     return q, sf
 
 
@@ -94,9 +115,9 @@ def rmsnorm_quantize_x(X, W, eps, reorder_index, KE):
         raise RuntimeError("W and reorder_index must have %d entries" % H)
     KE = int(KE)
     K = H + KE
-    with torch.cuda.device(X.device):
+    with _on(X.device):
         q = torch.empty((M, K // 2), dtype=torch.uint8, device=X.device)
-        sf = torch.empty((sf_bytes(M, K),), dtype=torch.uint8, device=X.device)
+        sf = torch.empty((_sf_bytes(M, K),), dtype=torch.uint8, device=X.device)
         rc = L.arcq_rmsnorm_quantize_x(X.data_ptr(), W.data_ptr(), float(eps), M, H, reorder_index.data_ptr(),
                                        KE, q.data_ptr(), sf.data_ptr(), _stream(X))
     _lib.check(rc, "arcq_rmsnorm_quantize_x")
@@ -127,7 +148,7 @@ def matmul(A, B, SFA, SFB, scale, out=None):
         alpha_dev = scale.data_ptr()
     else:
         alpha = float(scale)
-    with torch.cuda.device(A.device):
+    with _on(A.device):
         if out is None:
             out = torch.empty((M, N), dtype=torch.bfloat16, device=A.device)
         else:

@@ -102,6 +102,9 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       if (tl < p.num_tiles) issue_tile(s, tl);
     }
   }
+  if constexpr (RMS) {  // entries [KQ/16, 512) of the partial sums are never written: the tree reads them as zero
+    for (int i = tid; i < R * 512; i += THREADS) part[i] = 0.0f;
+  }
   if (tid < 128) {
     const float sf = e4m3_to_f32(tid < 127 ? tid : 126);
     sf_lut[tid] = sf;
@@ -210,10 +213,11 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     // ---- transpose the landed rows into the channel-major tile ----
     {
       const uint8_t *src = stage + (size_t)s * tile_bytes;
-      for (int u = tid; u < ((p.debug & 1) ? 0 : nunits); u += THREADS) {
-        uint4 in[R];
+      auto load_unit = [&](int u, uint4(&in)[R]) {
 #pragma unroll
         for (int lr = 0; lr < R; ++lr) in[lr] = *reinterpret_cast<const uint4 *>(src + (size_t)lr * rowbytes + (size_t)u * 16);
+      };
+      auto store_unit = [&](int u, const uint4(&in)[R]) {
         if constexpr (R == 1) {
           reinterpret_cast<uint4 *>(tile)[u] = in[0];
         } else {
@@ -232,6 +236,40 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
             else *reinterpret_cast<uint32_t *>(dst) = out[0];
           }
         }
+      };
+      if constexpr (RMS) {
+        // rmsnorm: the reference's thread tt sums channels 8tt..8tt+7 and then 8(bdx+tt)..+7 with one FMA chain
+        // (rmsnorm.cu:113-130) = exactly units tt and bdx+tt of this pass, so the sum of squares rides along
+        const int bdx = KQ / 16;
+        for (int tt = tid; tt < bdx; tt += THREADS) {
+          float acc[R];
+#pragma unroll
+          for (int lr = 0; lr < R; ++lr) acc[lr] = 0.0f;
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint4 in[R];
+            load_unit(half * bdx + tt, in);
+#pragma unroll
+            for (int lr = 0; lr < R; ++lr) {
+              const uint32_t w[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float lo = bf16lo_to_f32(w[i]), hi = bf16hi_to_f32(w[i]);
+                acc[lr] = __fmaf_rn(lo, lo, acc[lr]);
+                acc[lr] = __fmaf_rn(hi, hi, acc[lr]);
+              }
+            }
+            store_unit(half * bdx + tt, in);
+          }
+#pragma unroll
+          for (int lr = 0; lr < R; ++lr) part[lr * 512 + tt] = acc[lr];
+        }
+      } else {
+        for (int u = tid; u < ((p.debug & 1) ? 0 : nunits); u += THREADS) {
+          uint4 in[R];
+          load_unit(u, in);
+          store_unit(u, in);
+        }
       }
     }
     __syncthreads();
@@ -242,33 +280,8 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     // every thread has finished phase B of the previous tile (it passed the barrier above): its scale bytes are complete
     if (n > 0) copy_out_sf((n - 1) & 1, prev_blk, prev_t);
 
-    // ---- rmsnorm: sum of squares in the reference's exact order (rmsnorm.cu:113-157) ----
+    // ---- rmsnorm: the reference's reduction tree over the per-thread partial sums (rmsnorm.cu:131-157) ----
     if constexpr (RMS) {
-      const int bdx = KQ / 16;
-      for (int tt = tid; tt < 512; tt += THREADS) {
-        float acc[R];
-#pragma unroll
-        for (int lr = 0; lr < R; ++lr) acc[lr] = 0.0f;
-        if (tt < bdx) {
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int c = half * 8 * bdx + 8 * tt + i;
-              uint32_t v[RP];
-              lds_chunk<R>(tile + (size_t)chan_pos<R>(c) * CB, v);
-#pragma unroll
-              for (int lr = 0; lr < R; ++lr) {
-                const float f = (lr & 1) ? bf16hi_to_f32(v[lr >> 1]) : bf16lo_to_f32(v[lr >> 1]);
-                acc[lr] = __fmaf_rn(f, f, acc[lr]);
-              }
-            }
-          }
-        }
-#pragma unroll
-        for (int lr = 0; lr < R; ++lr) part[lr * 512 + tt] = acc[lr];
-      }
-      __syncthreads();
       if (warp < R) {  // one warp replays the reference's tree for one row (rmsnorm.cu:131-154)
         float *sp = part + warp * 512;
         for (int k = 0; k < 8; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 256];
@@ -473,7 +486,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   const int64_t blocks = ((int64_t)p.M + 127) / 128;
   const int wide = 512;  // 1024 threads (64 registers) measured slower than 512 on KQ=14336 (profiles/r1_quant_v3.log)
   // tile height, threads per CTA, CTAs per SM, staging slots -- first candidate that fits and gives every SM a tile
-  const Cfg cands[] = {{4, 256, 2, 2, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
+  const Cfg cands[] = {{4, 256, 2, 2, 4}, {4, 256, 2, 1, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
                        {1, wide, 1, 2, 1}, {1, wide, 1, 1, 1}};
   Cfg c{0, 0, 0, 0, 0};
   bool tab32 = false, own = false;
@@ -500,6 +513,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   if (c.R == RR && c.RT == RTT && c.threads == TH && c.minb == MB) \
     return launch_kind<RR, RTT, TH, MB>(p, flavour, is_w, rms, c.S, tab32, own, stream);
   ARCQ_T(4, 4, 256, 2) ARCQ_T(4, 4, 512, 1) ARCQ_T(2, 2, 256, 2) ARCQ_T(2, 2, 512, 1) ARCQ_T(1, 1, 512, 1)
+  ARCQ_T(2, 2, 256, 3) ARCQ_T(2, 2, 256, 4) ARCQ_T(4, 4, 256, 3)  // experiments: more CTAs per SM
   ARCQ_T(8, 8, 512, 1) ARCQ_T(8, 4, 512, 1)  // not chosen by default: measured within 4 % of the 4-row tile (r1_quant_cfg_sweep.log)
 #undef ARCQ_T
   return ARCQ_ENOSUP;
