@@ -46,6 +46,17 @@ template <int R> __device__ __forceinline__ int chan_pos(int c) {
   else return c ^ ((c >> 3) & (64 / R - 1));
 }
 
+// channel position for the matrix-transposed tile (quant_tma.cu): one stmatrix row (16 bytes) holds the chunks of the
+// 8/R channels {c, c+8, ...} of a 16- (R=4) or 32-channel (R=2) block; the row index is XOR-ed with the block number
+// and the position inside the row with the next block bits, so identity-like permutations gather without conflicts
+template <int R> __device__ __forceinline__ int chan_pos_m(int c) {
+  if constexpr (R == 4) { const int b = c >> 4; return (((b << 3) | ((c & 7) ^ (b & 7))) << 1) | (((c >> 3) ^ (c >> 7)) & 1); }
+  else if constexpr (R == 2) { const int b = c >> 5; return (((b << 3) | ((c & 7) ^ (b & 7))) << 2) | (((c >> 3) ^ (c >> 8)) & 3); }
+  else return chan_pos<R>(c);
+}
+// bytes added to every staged row so that the 8 row addresses of one ldmatrix fall into 8 different 16-byte bank groups
+__host__ __device__ constexpr int stage_pad(int R) { return R == 4 ? 32 : R == 2 ? 64 : 0; }
+
 // warp-specialised kernel family (quant_ws.cu); returns ARCQ_ENOSUP for shapes it does not take
 // TMA-staged kernel family (quant_tma.cu); same contract
 int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);

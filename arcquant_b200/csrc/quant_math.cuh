@@ -57,6 +57,52 @@ static __device__ __forceinline__ uint32_t quant16(const float (&x)[16], const f
   return sfb;
 }
 
+// (a0*b0, a1*b1) with one packed FP32 instruction (FMUL2, sm_100); each lane is an IEEE RN multiply like __fmul_rn
+static __device__ __forceinline__ void fmul2(float &d0, float &d1, float a0, float a1, float b0, float b1) {
+  uint64_t a, b, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
+
+// rmsnorm of two rows at once (rmsnorm.cu:165-171): v[i] = bf16x2 {row a, row b} of element i -> bf16((x * w) * rstd)
+static __device__ __forceinline__ void normalise16x2(uint32_t (&v)[16], const float (&wf)[16], float rstd_a, float rstd_b) {
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    float a = bf16lo_to_f32(v[i]), b = bf16hi_to_f32(v[i]);
+    fmul2(a, b, a, b, wf[i], wf[i]);
+    fmul2(a, b, a, b, rstd_a, rstd_b);
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(v[i]) : "f"(b), "f"(a));
+  }
+}
+
+// primary quantisation of two rows at once: v[i] = bf16x2 {row a (low half), row b (high half)} of element i.
+// Same arithmetic per row as quant16; the scaling multiply is one FMUL2 per element pair.
+static __device__ __forceinline__ void quant16x2(const uint32_t (&v)[16], const float *rcp_lut, uint32_t (&sfb)[2],
+                                                 uint32_t (&c)[2][2], float (&s)[2]) {
+  float xa[16], xb[16];
+  float ama = 0.0f, amb = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    xa[i] = bf16lo_to_f32(v[i]);
+    xb[i] = bf16hi_to_f32(v[i]);
+    ama = fmaxf(ama, fabsf(xa[i]));
+    amb = fmaxf(amb, fabsf(xb[i]));
+  }
+  s[0] = fmaxf(kScaleEps, fminf(kFp8Max, div6(ama)));
+  s[1] = fmaxf(kScaleEps, fminf(kFp8Max, div6(amb)));
+  sfb[0] = f32_to_e4m3(s[0]);
+  sfb[1] = f32_to_e4m3(s[1]);
+  const float ra = rcp_lut[sfb[0]], rb = rcp_lut[sfb[1]];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) fmul2(xa[i], xb[i], xa[i], xb[i], ra, rb);
+  c[0][0] = f32x8_to_e2m1(xa[0], xa[1], xa[2], xa[3], xa[4], xa[5], xa[6], xa[7]);
+  c[0][1] = f32x8_to_e2m1(xa[8], xa[9], xa[10], xa[11], xa[12], xa[13], xa[14], xa[15]);
+  c[1][0] = f32x8_to_e2m1(xb[0], xb[1], xb[2], xb[3], xb[4], xb[5], xb[6], xb[7]);
+  c[1][1] = f32x8_to_e2m1(xb[8], xb[9], xb[10], xb[11], xb[12], xb[13], xb[14], xb[15]);
+}
+
 // residual of 16 values: e = bf16(x - deq(code) * sub) (reorder.cu:157-160 / :474), then quantised again
 static __device__ __forceinline__ uint32_t residual16(const float (&x)[16], uint32_t c_lo, uint32_t c_hi, float sub,
                                                const float *rcp_lut, uint32_t &r_lo, uint32_t &r_hi) {

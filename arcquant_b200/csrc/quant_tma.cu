@@ -39,7 +39,7 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
   c.rstd = o; if (rms) o += 64;
   o = (o + 127) & ~127;
   c.tile = o; o += KQ * 2 * R;
-  c.stage = o; o += S * KQ * 2 * R;
+  c.stage = o; o += S * (KQ * 2 + stage_pad(R)) * R;
   c.total = o;
   return c;
 }
@@ -63,13 +63,16 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
   uint8_t *arcs = smem + cv.arc;
   uint8_t *tile = smem + cv.tile;
   uint8_t *stage = smem + cv.stage;
-  const uint32_t rowbytes = (uint32_t)KQ * 2;
-  const int tile_bytes = KQ * CB;
+  constexpr bool MATX = !RMS && (R == 4 || R == 2);  // transpose with ldmatrix.trans + stmatrix
+  const uint32_t rowbytes = (uint32_t)KQ * 2, rowstride = rowbytes + stage_pad(R);
+  const int tile_bytes = KQ * CB, slot_bytes = R * (int)rowstride;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   float *part = reinterpret_cast<float *>(smem + cv.part), *rstd_s = reinterpret_cast<float *>(smem + cv.rstd);
   const uint16_t *wtab = reinterpret_cast<const uint16_t *>(smem + cv.wtab);
 
-  // one thread streams the rows of tile `tile_id` into staging slot s
+  // called by every lane of ONE warp with warp-uniform arguments: the address arithmetic stays on the uniform datapath
+  // and one elected lane streams the rows of tile `tile_id` into staging slot s
+  constexpr int IW = (RMS && THREADS / 32 > R) ? R : 0;  // issuing warp: not one of the rmsnorm tree warps
   auto issue_tile = [&](int s, int tile_id) {
     const int blk = tile_id / TPB, t = tile_id % TPB;
     const int r0 = blk * 128 + TileMap<R>::row(t, 0);
@@ -77,13 +80,16 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     int nv = 0;
 #pragma unroll
     for (int lr = 0; lr < R; ++lr) nv += TileMap<R>::row(0, lr) < mrows ? 1 : 0;
-    ptx::mbar_arrive_expect_tx(&full[s], (uint32_t)nv * rowbytes);
     const uint8_t *src = reinterpret_cast<const uint8_t *>(p.x) + (int64_t)r0 * rowbytes;
-    uint8_t *dst = stage + (size_t)s * tile_bytes;
+    uint8_t *dst = stage + (size_t)s * slot_bytes;
+    if (ptx::elect_one()) {
+      ptx::mbar_arrive_expect_tx(&full[s], (uint32_t)nv * rowbytes);
 #pragma unroll
-    for (int lr = 0; lr < R; ++lr)
-      if (TileMap<R>::row(0, lr) < mrows)
-        ptx::bulk_load(dst + (size_t)lr * rowbytes, src + (size_t)TileMap<R>::row(0, lr) * rowbytes, rowbytes, &full[s]);
+      for (int lr = 0; lr < R; ++lr)
+        if (TileMap<R>::row(0, lr) < mrows)
+          ptx::bulk_load(dst + (size_t)lr * rowstride, src + (size_t)TileMap<R>::row(0, lr) * rowbytes, rowbytes, &full[s]);
+    }
+    __syncwarp();
   };
 
   // ---- one-time setup: barriers, LUTs, gather-offset table ----
@@ -92,11 +98,11 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     ptx::fence_barrier_init();
   }
   if (p.M % 128) {  // a ragged last block leaves rows of some slots unwritten: give them defined (zero) content
-    for (int i = tid; i < S * tile_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < S * slot_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
     ptx::fence_proxy_async();
   }
   __syncthreads();
-  if (tid == 0) {
+  if (warp == IW) {
     for (int s = 0; s < S; ++s) {
       const int tl = blockIdx.x + s * gridDim.x;
       if (tl < p.num_tiles) issue_tile(s, tl);
@@ -116,8 +122,8 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     uint32_t pos[8];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      pos[2 * i] = (uint32_t)chan_pos<R>((int)(ww[i] & 0xffffu));
-      pos[2 * i + 1] = (uint32_t)chan_pos<R>((int)(ww[i] >> 16));
+      pos[2 * i] = (uint32_t)(MATX ? chan_pos_m<R>((int)(ww[i] & 0xffffu)) : chan_pos<R>((int)(ww[i] & 0xffffu)));
+      pos[2 * i + 1] = (uint32_t)(MATX ? chan_pos_m<R>((int)(ww[i] >> 16)) : chan_pos<R>((int)(ww[i] >> 16)));
     }
     if constexpr (TAB32) {
       uint4 *dst = reinterpret_cast<uint4 *>(smem + cv.tab) + 2 * u;
@@ -212,10 +218,10 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
     // ---- transpose the landed rows into the channel-major tile ----
     {
-      const uint8_t *src = stage + (size_t)s * tile_bytes;
+      const uint8_t *src = stage + (size_t)s * slot_bytes;
       auto load_unit = [&](int u, uint4(&in)[R]) {
 #pragma unroll
-        for (int lr = 0; lr < R; ++lr) in[lr] = *reinterpret_cast<const uint4 *>(src + (size_t)lr * rowbytes + (size_t)u * 16);
+        for (int lr = 0; lr < R; ++lr) in[lr] = *reinterpret_cast<const uint4 *>(src + (size_t)lr * rowstride + (size_t)u * 16);
       };
       auto store_unit = [&](int u, const uint4(&in)[R]) {
         if constexpr (R == 1) {
@@ -264,6 +270,39 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 #pragma unroll
           for (int lr = 0; lr < R; ++lr) part[lr * 512 + tt] = acc[lr];
         }
+      } else if constexpr (MATX) {
+        // a warp step moves 256/R channels x R rows: matrix m = channels [CW k + MC m, +MC); its 8 rows are the R tile
+        // rows of each of the 8/R 8-channel blocks; transposed, row i of the stored matrix is the 16 bytes
+        // {chunk of channel 8 hb + i : hb} = chan_pos_m.  k = warp + NW it keeps the swizzle terms per-warp constants.
+        constexpr int NW = THREADS / 32, CW = 256 / R, MC = CW / 4, HB = 8 / R;
+        static_assert(NW % 8 == 0, "swizzle terms must not depend on the iteration");
+        const int m = lane >> 3, r = lane & 7;
+        const uint32_t src_s = ptx::smem_u32(src), tile_s = ptx::smem_u32(tile);
+        auto ld_addr = [&](int k) {
+          const int hsw = (k >> 1) & (HB - 1);
+          return src_s + (uint32_t)(r % R) * rowstride + (uint32_t)(k * CW + m * MC + 8 * ((r / R) ^ hsw)) * 2;
+        };
+        auto st_addr = [&](int k) {
+          const int b = 4 * k + m;
+          return tile_s + (uint32_t)((b * 8 + (r ^ (b & 7))) * 16);
+        };
+        const int nch = (p.debug & 1) ? 0 : KQ / CW;
+        uint32_t la = ld_addr(warp), sa = st_addr(warp);
+#pragma unroll 4
+        for (int k = warp; k < nch; k += NW) {
+          uint32_t f[4];
+          ptx::ldsm_x4_t(la, f);
+          ptx::stsm_x4(sa, f);
+          la += NW * CW * 2;
+          sa += NW * CW * CB;
+        }
+        if constexpr (R == 2) {  // KQ = 64 (mod 128): the last half step has two matrices
+          if ((KQ & 64) && warp == nch % NW && !(p.debug & 1)) {
+            uint32_t f[4];
+            ptx::ldsm_x2_t(ld_addr(nch), f);
+            ptx::stsm_x2(st_addr(nch), f);
+          }
+        }
       } else {
         for (int u = tid; u < ((p.debug & 1) ? 0 : nunits); u += THREADS) {
           uint4 in[R];
@@ -273,7 +312,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       }
     }
     __syncthreads();
-    if (tid == 0) {  // slot s has been read by everyone: refill it with the tile S steps ahead
+    if (warp == IW) {  // slot s has been read by everyone: refill it with the tile S steps ahead
       const int tl = tile_id + S * gridDim.x;
       if (tl < p.num_tiles) issue_tile(s, tl);
     }
@@ -283,14 +322,19 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     // ---- rmsnorm: the reference's reduction tree over the per-thread partial sums (rmsnorm.cu:131-157) ----
     if constexpr (RMS) {
       if (warp < R) {  // one warp replays the reference's tree for one row (rmsnorm.cu:131-154)
-        float *sp = part + warp * 512;
-        for (int k = 0; k < 8; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 256];
-        __syncwarp();
-        for (int k = 0; k < 4; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 128];
-        __syncwarp();
-        for (int k = 0; k < 2; ++k) sp[lane + 32 * k] += sp[lane + 32 * k + 64];
-        __syncwarp();
-        float v = sp[lane] + sp[lane + 32];
+        // strides 256, 128, 64 and the final s[t] + s[t+32] pair element t with t + 32 k: all in the same lane, so the
+        // whole shared-memory tree is 15 register adds per lane in the reference's association order
+        const float *sp = part + warp * 512;
+        float a[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) a[k] = sp[lane + 32 * k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = __fadd_rn(a[k], a[k + 8]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k] = __fadd_rn(a[k], a[k + 4]);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) a[k] = __fadd_rn(a[k], a[k + 2]);
+        float v = __fadd_rn(a[0], a[1]);
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
         if (lane == 0) rstd_s[warp] = rsqrtf(__fadd_rn(__fdiv_rn(v, (float)KQ), p.eps));  // :157
@@ -326,27 +370,12 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       const int drb = TileMap<R>::row(0, rb * RT);  // row(0, rb*RT + lr) = row(0, rb*RT) + row(0, lr) for every TileMap
       uint8_t *qg = qbase + 8 * slot_p + (uint32_t)drb * khalf;
       const int mr = mrows - drb;
-#pragma unroll
-      for (int lr = 0; lr < RT; ++lr) {
-        float x[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          x[i] = (lr & 1) ? bf16hi_to_f32(v[i][lr >> 1]) : bf16lo_to_f32(v[i][lr >> 1]);
-          if constexpr (RMS)  // rmsnorm.cu:165-171: bf16((x * w) * rstd), left to right
-            x[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmul_rn(__fmul_rn(x[i], wf[i]), rstd_s[rb * RT + lr])));
-        }
-        uint32_t c_lo, c_hi;
-        float sc;
-        uint32_t sfb;
-        if (p.debug & 4) { sfb = __float_as_uint(x[0]) >> 24; c_lo = __float_as_uint(x[1]); c_hi = __float_as_uint(x[15]); sc = x[2]; }
-        else sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
+      // store one quantised row: scale byte, codes, and (activations) the residual work item of an ARC group
+      auto emit_row = [&](int lr, uint32_t sfb, uint32_t c_lo, uint32_t c_hi, float sc, const uint32_t(&xb)[8]) {
         sfp[4 * lr] = (uint8_t)sfb;
         if (IS_W && arc) sfp[4 * lr + ((dslot >> 2) * (4 * R) + (dslot & 3))] = (uint8_t)sfb;  // reorder.cu:307-316
         if (!IS_W && arc) {  // hand the residual work of this (group,row) to phase B: values, codes, subtrahend scale
           uint4 *a = reinterpret_cast<uint4 *>(arcs + ((g - G) * R + rb * RT + lr) * 48);
-          uint32_t xb[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
           a[0] = make_uint4(xb[0], xb[1], xb[2], xb[3]);
           a[1] = make_uint4(xb[4], xb[5], xb[6], xb[7]);
           // 16-wide: rounded scale (reorder.cu:157); 32-wide: unrounded (reorder.cu:474)
@@ -356,6 +385,49 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
         if (TileMap<R>::row(0, lr) < mr) {
           __stcs(reinterpret_cast<uint2 *>(qp), make_uint2(c_lo, c_hi));
           if (IS_W && arc) __stcs(reinterpret_cast<uint2 *>(qp + 8 * dslot), make_uint2(c_lo, c_hi));
+        }
+      };
+      // two rows per step with packed FP32 multiplies: measured faster for the rmsnorm variant (-6..9 %) and for 2-row
+      // items (-7 %), slower for plain 4-row items (+17 %)  (profiles/r1_quant_packed_ab.log)
+      constexpr bool kPacked2 = (RT % 2 == 0) && (RMS || RT == 2);
+      if constexpr (kPacked2) {
+        // two rows per step: the chunk word w2 holds rows 2 w2 (low halves) and 2 w2 + 1 (high halves) of every channel
+#pragma unroll
+        for (int w2 = 0; w2 < RT / 2; ++w2) {
+          uint32_t pv[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pv[i] = v[i][w2];
+          if constexpr (RMS) normalise16x2(pv, wf, rstd_s[rb * RT + 2 * w2], rstd_s[rb * RT + 2 * w2 + 1]);
+          uint32_t sfb[2], c[2][2];
+          float sc[2];
+          quant16x2(pv, rcp_lut, sfb, c, sc);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t xb[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(pv[2 * i], pv[2 * i + 1], h ? 0x7632 : 0x5410);
+            emit_row(2 * w2 + h, sfb[h], c[h][0], c[h][1], sc[h], xb);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int lr = 0; lr < RT; ++lr) {
+          float x[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            x[i] = (lr & 1) ? bf16hi_to_f32(v[i][lr >> 1]) : bf16lo_to_f32(v[i][lr >> 1]);
+            if constexpr (RMS)  // rmsnorm.cu:165-171: bf16((x * w) * rstd), left to right
+              x[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmul_rn(__fmul_rn(x[i], wf[i]), rstd_s[rb * RT + lr])));
+          }
+          uint32_t c_lo, c_hi;
+          float sc;
+          uint32_t sfb;
+          if (p.debug & 4) { sfb = __float_as_uint(x[0]) >> 24; c_lo = __float_as_uint(x[1]); c_hi = __float_as_uint(x[15]); sc = x[2]; }
+          else sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
+          uint32_t xb[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
+          emit_row(lr, sfb, c_lo, c_hi, sc, xb);
         }
       }
       if constexpr (OWN) break;  // THREADS >= items: one item per thread, its offsets stay in registers

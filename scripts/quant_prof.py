@@ -21,6 +21,7 @@ def main():
                                                     "8192,28672,1024", "8192,8192,512", "2048,4096,256", "512,4096,256"])
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--rms", action="store_true")
+    ap.add_argument("--identity", action="store_true", help="identity reorder_index: conflict-free gather (upper bound)")
     args = ap.parse_args()
     peak = 6540.0
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -34,6 +35,8 @@ def main():
         nbuf = max(2, int(400e6 // (M * KQ * 2)) + 1)
         xs = [(torch.randn(M, KQ, generator=g) * 50).to(torch.bfloat16).to(dev) for _ in range(min(nbuf, 8))]
         idx = torch.randperm(KQ, generator=g).to(torch.int16).to(dev)
+        if args.identity:
+            idx = torch.arange(KQ, dtype=torch.int16, device=dev)
         w = torch.ones(KQ, dtype=torch.bfloat16, device=dev)
         rms = args.rms and 2048 <= KQ <= 8192
 
