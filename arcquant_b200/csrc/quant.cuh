@@ -52,10 +52,11 @@ template <int R> __device__ __forceinline__ int chan_pos(int c) {
 template <int R> __device__ __forceinline__ int chan_pos_m(int c) {
   if constexpr (R == 4) { const int b = c >> 4; return (((b << 3) | ((c & 7) ^ (b & 7))) << 1) | (((c >> 3) ^ (c >> 7)) & 1); }
   else if constexpr (R == 2) { const int b = c >> 5; return (((b << 3) | ((c & 7) ^ (b & 7))) << 2) | (((c >> 3) ^ (c >> 8)) & 3); }
+  else if constexpr (R == 8) { const int b = c >> 3; return (b << 3) | ((c & 7) ^ (b & 7)); }  // one 16-byte chunk per stmatrix row
   else return chan_pos<R>(c);
 }
 // bytes added to every staged row so that the 8 row addresses of one ldmatrix fall into 8 different 16-byte bank groups
-__host__ __device__ constexpr int stage_pad(int R) { return R == 4 ? 32 : R == 2 ? 64 : 0; }
+__host__ __device__ constexpr int stage_pad(int R) { return R == 8 ? 16 : R == 4 ? 32 : R == 2 ? 64 : 0; }
 
 // warp-specialised kernel family (quant_ws.cu); returns ARCQ_ENOSUP for shapes it does not take
 // TMA-staged kernel family (quant_tma.cu); same contract

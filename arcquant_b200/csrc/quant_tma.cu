@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
   uint8_t *arcs = smem + cv.arc;
   uint8_t *tile = smem + cv.tile;
   uint8_t *stage = smem + cv.stage;
-  constexpr bool MATX = !RMS && (R == 4 || R == 2);  // transpose with ldmatrix.trans + stmatrix
+  constexpr bool MATX = !RMS && (R == 8 || R == 4 || R == 2);  // transpose with ldmatrix.trans + stmatrix
   const uint32_t rowbytes = (uint32_t)KQ * 2, rowstride = rowbytes + stage_pad(R);
   const int tile_bytes = KQ * CB, slot_bytes = R * (int)rowstride;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
         // a warp step moves 256/R channels x R rows: matrix m = channels [CW k + MC m, +MC); its 8 rows are the R tile
         // rows of each of the 8/R 8-channel blocks; transposed, row i of the stored matrix is the 16 bytes
         // {chunk of channel 8 hb + i : hb} = chan_pos_m.  k = warp + NW it keeps the swizzle terms per-warp constants.
-        constexpr int NW = THREADS / 32, CW = 256 / R, MC = CW / 4, HB = 8 / R;
+        constexpr int NW = THREADS / 32, CW = 256 / R, MC = CW / 4, HB = R == 8 ? 1 : 8 / R;
         static_assert(NW % 8 == 0, "swizzle terms must not depend on the iteration");
         const int m = lane >> 3, r = lane & 7;
         const uint32_t src_s = ptx::smem_u32(src), tile_s = ptx::smem_u32(tile);
@@ -558,7 +558,10 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   const int64_t blocks = ((int64_t)p.M + 127) / 128;
   const int wide = 512;  // 1024 threads (64 registers) measured slower than 512 on KQ=14336 (profiles/r1_quant_v3.log)
   // tile height, threads per CTA, CTAs per SM, staging slots -- first candidate that fits and gives every SM a tile
-  const Cfg cands[] = {{4, 256, 2, 2, 4}, {4, 256, 2, 1, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
+  // 8-row tiles with two threads per 16-group (16-byte chunks: 8 random chunks per shared-memory wavefront instead of
+  // 16, scale bytes leave as whole 32-byte sectors) measured 5-7 % faster than 4-row tiles at two CTAs per SM where
+  // every thread owns one item (profiles/r1_quant_r8_sweep.log)
+  const Cfg cands[] = {{8, 512, 1, 1, 4}, {4, 256, 2, 2, 4}, {4, 256, 2, 1, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
                        {1, wide, 1, 2, 1}, {1, wide, 1, 1, 1}};
   Cfg c{0, 0, 0, 0, 0};
   bool tab32 = false, own = false;
@@ -570,6 +573,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   if (c.R == 0) {
     for (const Cfg &k : cands) {
       if (rms && k.threads < 32 * k.R) continue;
+      if (k.R == 8 && ngroups * (k.R / k.RT) > k.threads) continue;  // only with one owned item per thread
       const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
       if (need * k.minb > kSmemPerSm) continue;
       if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;

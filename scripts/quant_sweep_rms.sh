@@ -1,0 +1,5 @@
+for cfg in "$@"; do
+  echo "cfg $cfg"
+  if [ "$cfg" = "-" ]; then unset ARCQ_QUANT_TMA; else export ARCQ_QUANT_TMA=$cfg; fi
+  timeout 100 python scripts/quant_prof.py --rms --shapes 32768,4096,256 8192,4096,256 8192,3584,256 2>&1 | grep quant
+done

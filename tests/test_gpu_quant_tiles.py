@@ -39,6 +39,10 @@ TILE_CASES = [
     ("2,512,1,2,1", 130, 18944, 512, None),
     ("1,512,1,1,1", 100, 28672, 1024, None),
     ("8,512,1,8,1", 260, 4096, 256, None),    # 8-row tiles (not chosen by default)
+    ("8,512,2,4,1", 300, 4096, 256, None),    # 8-row tiles, two threads per group
+    ("8,512,1,4,1", 1290, 4096, 256, None),   # the default for KQ <= 4096 at prefill sizes
+    ("8,512,1,4,1", 200, 3584, 256, None),
+    ("8,512,1,4,1", 150, 2048, 0, None),
 ]
 
 
@@ -54,7 +58,7 @@ def test_forced_tile_quantize_x(monkeypatch, knob, M, KQ, KE, flavour):
     _check(q, sf, q_ref, sf_ref, M, KQ + KE, "quantize_x %s M=%d KQ=%d KE=%d" % (knob, M, KQ, KE))
 
 
-@pytest.mark.parametrize("knob,N,KQ,KE", [("4,256,2,4,2", 520, 4096, 256), ("2,512,2,2,1", 260, 14336, 512),
+@pytest.mark.parametrize("knob,N,KQ,KE", [("4,256,2,4,2", 520, 4096, 256), ("8,512,1,4,1", 300, 4096, 256), ("2,512,2,2,1", 260, 14336, 512),
                                           ("4,512,2,4,1", 300, 8192, 512)])
 def test_forced_tile_quantize_w(monkeypatch, knob, N, KQ, KE):
     from arcquant_b200 import agemm
@@ -79,7 +83,7 @@ def test_default_dispatch_at_prefill_sizes(M, KQ, KE):
     _check(q, sf, q_ref, sf_ref, M, KQ + KE, "quantize_x default M=%d KQ=%d KE=%d" % (M, KQ, KE))
 
 
-RMS_CASES = [("4,256,1,4,2", 1300, 4096, 256), ("4,256,1,4,2", 200, 3584, 256), ("4,512,1,4,1", 300, 8192, 512),
+RMS_CASES = [("8,512,1,4,1", 1300, 4096, 256), ("8,512,1,4,1", 140, 3584, 256), ("4,256,1,4,2", 1300, 4096, 256), ("4,256,1,4,2", 200, 3584, 256), ("4,512,1,4,1", 300, 8192, 512),
              ("2,512,2,2,1", 300, 8192, 512), ("4,256,2,4,2", 260, 2048, 128), ("2,256,2,2,2", 150, 5120, 64)]
 
 
