@@ -66,6 +66,15 @@ static __device__ __forceinline__ void fmul2(float &d0, float &d1, float a0, flo
   asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
 }
 
+// (a0*a0 + c0, a1*a1 + c1) with one packed FFMA2: two independent IEEE RN fused multiply-adds like __fmaf_rn
+static __device__ __forceinline__ void fsqacc2(float &c0, float &c1, float a0, float a1) {
+  uint64_t a, c;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+  asm("fma.rn.f32x2 %0, %1, %1, %0;" : "+l"(c) : "l"(a));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(c0), "=f"(c1) : "l"(c));
+}
+
 // rmsnorm of two rows at once (rmsnorm.cu:165-171): v[i] = bf16x2 {row a, row b} of element i -> bf16((x * w) * rstd)
 static __device__ __forceinline__ void normalise16x2(uint32_t (&v)[16], const float (&wf)[16], float rstd_a, float rstd_b) {
 #pragma unroll

@@ -255,14 +255,27 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           for (int half = 0; half < 2; ++half) {
             uint4 in[R];
             load_unit(half * bdx + tt, in);
+            if constexpr (R % 2 == 0) {  // two rows per packed FFMA2, each row's chain in the reference's order
 #pragma unroll
-            for (int lr = 0; lr < R; ++lr) {
-              const uint32_t w[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w};
+              for (int lr = 0; lr < R; lr += 2) {
+                const uint32_t wa[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w};
+                const uint32_t wb[4] = {in[lr + 1].x, in[lr + 1].y, in[lr + 1].z, in[lr + 1].w};
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float lo = bf16lo_to_f32(w[i]), hi = bf16hi_to_f32(w[i]);
-                acc[lr] = __fmaf_rn(lo, lo, acc[lr]);
-                acc[lr] = __fmaf_rn(hi, hi, acc[lr]);
+                for (int i = 0; i < 4; ++i) {
+                  fsqacc2(acc[lr], acc[lr + 1], bf16lo_to_f32(wa[i]), bf16lo_to_f32(wb[i]));
+                  fsqacc2(acc[lr], acc[lr + 1], bf16hi_to_f32(wa[i]), bf16hi_to_f32(wb[i]));
+                }
+              }
+            } else {
+#pragma unroll
+              for (int lr = 0; lr < R; ++lr) {
+                const uint32_t w[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float lo = bf16lo_to_f32(w[i]), hi = bf16hi_to_f32(w[i]);
+                  acc[lr] = __fmaf_rn(lo, lo, acc[lr]);
+                  acc[lr] = __fmaf_rn(hi, hi, acc[lr]);
+                }
               }
             }
             store_unit(half * bdx + tt, in);
@@ -561,7 +574,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   // 8-row tiles with two threads per 16-group (16-byte chunks: 8 random chunks per shared-memory wavefront instead of
   // 16, scale bytes leave as whole 32-byte sectors) measured 5-7 % faster than 4-row tiles at two CTAs per SM where
   // every thread owns one item (profiles/r1_quant_r8_sweep.log)
-  const Cfg cands[] = {{8, 512, 1, 1, 4}, {4, 256, 2, 2, 4}, {4, 256, 2, 1, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
+  const Cfg cands[] = {{8, 512, 1, 1, 4}, {4, 256, 2, 2, 4}, {4, 256, 2, 1, 4}, {4, 512, 1, 1, 4}, {4, 512, 1, 2, 4}, {2, 256, 2, 2, 2}, {2, wide, 1, 2, 2}, {2, wide, 1, 1, 2},
                        {1, wide, 1, 2, 1}, {1, wide, 1, 1, 1}};
   Cfg c{0, 0, 0, 0, 0};
   bool tab32 = false, own = false;
@@ -574,6 +587,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     for (const Cfg &k : cands) {
       if (rms && k.threads < 32 * k.R) continue;
       if (k.R == 8 && ngroups * (k.R / k.RT) > k.threads) continue;  // only with one owned item per thread
+      if (k.R == 4 && k.threads == 256 && ngroups > 256) continue;   // two passes per tile: the wide CTA owns its items
       const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
       if (need * k.minb > kSmemPerSm) continue;
       if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;
