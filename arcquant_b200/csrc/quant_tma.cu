@@ -31,6 +31,9 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
   c.sfs = o; o += 2 * ((KQ + KE) / 64) * 4 * R;  // two scale staging buffers [chunk][lr][slot%4]
   o = (o + 15) & ~15;
   c.arc = o; o += (KE / 16) * R * 48;            // per ARC (group,row): 16 bf16 x, 2 code words, subtrahend scale
+#ifdef ARCQ_STASH_LRMAJOR
+  o += R * 16;  // experiment: [row][group] stash, rows padded by 16 bytes (conflict-free STS.128 and LDS.128)
+#endif
   c.tab = o; o += KQ * (tab32 ? 4 : 2);
   o = (o + 15) & ~15;
   c.wtab = o; if (rms) o += KQ * 2;
@@ -388,7 +391,11 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
         sfp[4 * lr] = (uint8_t)sfb;
         if (IS_W && arc) sfp[4 * lr + ((dslot >> 2) * (4 * R) + (dslot & 3))] = (uint8_t)sfb;  // reorder.cu:307-316
         if (!IS_W && arc) {  // hand the residual work of this (group,row) to phase B: values, codes, subtrahend scale
+#ifdef ARCQ_STASH_LRMAJOR
+          uint4 *a = reinterpret_cast<uint4 *>(arcs + (rb * RT + lr) * ((KE / 16) * 48 + 16) + (g - G) * 48);
+#else
           uint4 *a = reinterpret_cast<uint4 *>(arcs + ((g - G) * R + rb * RT + lr) * 48);
+#endif
           a[0] = make_uint4(xb[0], xb[1], xb[2], xb[3]);
           a[1] = make_uint4(xb[4], xb[5], xb[6], xb[7]);
           // 16-wide: rounded scale (reorder.cu:157); 32-wide: unrounded (reorder.cu:474)
@@ -452,8 +459,13 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 #ifndef ARCQ_PHASEB_QUAD  // one thread per (group,row) item; the 4-lanes-per-item variant below measured 5 % slower (r1l_quant.log)
       const int nitems = (p.debug & 8) ? 0 : (KE / 16) * R;
       for (int item = tid; item < nitems; item += THREADS) {
+#ifdef ARCQ_STASH_LRMAJOR
+        const int nper = KE / 16, lr = item / nper, g = G + item % nper;
+        const uint4 *a = reinterpret_cast<const uint4 *>(arcs + lr * (nper * 48 + 16) + (g - G) * 48);
+#else
         const int g = G + item / R, lr = item % R;
         const uint4 *a = reinterpret_cast<const uint4 *>(arcs + item * 48);
+#endif
         const uint4 x0 = a[0], x1 = a[1], cs = a[2];
         const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
         float x[16];
