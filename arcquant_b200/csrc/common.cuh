@@ -19,6 +19,36 @@ namespace arcq {
 void set_error(const char *fmt, ...);
 void count_launch(int n = 1);
 int sm_count();  // SMs of the current device (cached), <= 0 on error
+int current_device();  // cudaGetDevice clamped to [0, kMaxDevices), -1 on error
+
+constexpr int kMaxDevices = 64;
+
+// Tuning overrides set through arcq_set_option() (include/arcq.h).  They only select among kernels / tile shapes that
+// all compute the same result (the parity tests force each one through this); nothing here can skip work.  Plain
+// process-wide values read at launch time: no environment lookups on the launch path.
+struct Options {
+  int quant_tile[5];   // {R, threads, S, RT, CTAs/SM} of the TMA-staged quantise kernel; R == 0: shape-driven choice
+  int quant_family;    // 3 = TMA-staged kernel (default), 1 = single-role fallback kernel of quant.cu
+  int gemm_pair;       // -1 = by shape, 0 = never, 1 = always use the cta_group::2 kernel
+  int gemm_bn;         // 0 = by shape, 128 / 256 = tile width of the single-CTA kernel
+  int gemm_splitk;     // -1 = by shape, 0 = never, >= 2 = forced number of K splits of the small-M kernel
+};
+Options &options();
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per (function, DEVICE): cache what was set per device so that a
+// second GPU driven from the same process gets its own opt-in (and host threads racing here only repeat an idempotent call)
+struct SmemAttrCache { int set[kMaxDevices]; };
+template <typename Kern>
+inline int ensure_dynamic_smem(Kern kern, int bytes, SmemAttrCache &cache) {
+  const int dev = current_device();
+  if (dev < 0) return ARCQ_ECUDA;
+  if (bytes > cache.set[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(%d B) failed: %s", bytes, cudaGetErrorString(e)); return ARCQ_ECUDA; }
+    cache.set[dev] = bytes;
+  }
+  return ARCQ_OK;
+}
 
 #define ARCQ_CUDA_TRY(expr)                                                          \
   do {                                                                               \

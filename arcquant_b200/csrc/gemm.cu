@@ -57,10 +57,11 @@ struct GemmParams {
   const uint8_t *sfb;
   __nv_bfloat16 *d;
   const float *alpha_dev;
+  const float *col_scale;  // nullable fp32 [N]: column n is scaled by RN(alpha * col_scale[n])
   float alpha;
   int M, N, K;
+  int64_t ldd;             // row stride of d in elements
   int tiles_m, tiles_n;
-  int debug;  // experiments only: bit0 = skip TMA loads, bit1 = skip MMA issue, bit2 = skip UTCCP, bit3 = skip stores
 };
 
 template <int BN, int STAGES, int PC>
@@ -124,18 +125,14 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (kchunks > 4) kchunks = 4;
           const uint32_t sf_bytes = (uint32_t)kchunks * 512u;
           if (ptx::elect_one()) {
-            if (p.debug & 1) {
-              ptx::mbar_arrive(&full[s]);
-            } else {
-              ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + sf_bytes * (1 + nsfb));
-              ptx::tma_load_2d(st, &tmap_a, kb * kBKBytes, m0, &full[s]);
-              ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, n0, &full[s]);
-              ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)mt * kc_total + kb * 4) * 512, sf_bytes,
-                             &full[s]);
-              for (int j = 0; j < nsfb; ++j)
-                ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + j * 2048,
-                               p.sfb + ((size_t)(nt * Cfg::NB + j) * kc_total + kb * 4) * 512, sf_bytes, &full[s]);
-            }
+            ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + sf_bytes * (1 + nsfb));
+            ptx::tma_load_2d(st, &tmap_a, kb * kBKBytes, m0, &full[s]);
+            ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kBKBytes, n0, &full[s]);
+            ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)mt * kc_total + kb * 4) * 512, sf_bytes,
+                           &full[s]);
+            for (int j = 0; j < nsfb; ++j)
+              ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SFA_BYTES + j * 2048,
+                             p.sfb + ((size_t)(nt * Cfg::NB + j) * kc_total + kb * 4) * 512, sf_bytes, &full[s]);
           }
           __syncwarp();
         }
@@ -169,23 +166,19 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const uint64_t b_desc = ptx::make_sw128_kmajor_desc(b_addr);
           if (ptx::elect_one()) {
           for (int c = 0; c < kchunks; ++c) {
-            if (!(p.debug & 4)) {
-              ptx::tc_cp_32x128b_warpx4(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
+            ptx::tc_cp_32x128b_warpx4(sfa_t + c * 4, ptx::make_sf_desc(sfa_addr + c * 512));
 #pragma unroll
-              for (int j = 0; j < Cfg::NB; ++j)
-                ptx::tc_cp_32x128b_warpx4(sfb_t + c * 4 * Cfg::NB + j * 4, ptx::make_sf_desc(sfb_addr + j * 2048 + c * 512));
-            }
+            for (int j = 0; j < Cfg::NB; ++j)
+              ptx::tc_cp_32x128b_warpx4(sfb_t + c * 4 * Cfg::NB + j * 4, ptx::make_sf_desc(sfb_addr + j * 2048 + c * 512));
             // advance 32 bytes (64 e2m1) inside the 128-B swizzle span: +2 in the 16-B address field
-            if (!(p.debug & 2))
-              ptx::tc_mma_nvfp4(d_tmem, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
-                                sfa_t + c * 4, sfb_t + c * 4 * Cfg::NB);
+            ptx::tc_mma_nvfp4(d_tmem, a_desc + 2 * c, b_desc + 2 * c, idesc, (kb > 0 || c > 0) ? 1u : 0u,
+                              sfa_t + c * 4, sfb_t + c * 4 * Cfg::NB);
           }
-          if (p.debug & 16) ptx::mbar_arrive(&empty[s]); else
           ptx::tc_commit(&empty[s]);  // frees the smem stage once these MMAs have read it
           }
           __syncwarp();
         }
-        if (ptx::elect_one()) { if (p.debug & 16) ptx::mbar_arrive(&tfull[acc]); else ptx::tc_commit(&tfull[acc]); }  // accumulator complete -> epilogue
+        if (ptx::elect_one()) ptx::tc_commit(&tfull[acc]);  // accumulator complete -> epilogue
         __syncwarp();
       }
     }
@@ -198,7 +191,8 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint8_t *wst = epi + (warp - 2) * Cfg::EPI_WARP_BYTES;
     constexpr int CH = PC / 8;        // 16-byte chunks per staged row
     constexpr int RB = PC * 2;        // staged row bytes
-    const bool vec_ok = (p.N % 8) == 0;
+    const bool vec_ok = (p.N % 8) == 0 && (p.ldd % 8) == 0;
+    const float *cs = p.col_scale;
     uint32_t tile_it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tile_it) {
       const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
@@ -208,15 +202,12 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + half * HC;
       uint32_t r[HC / 32][32];
-      if (!(p.debug & 32)) {
 #pragma unroll
       for (int cb = 0; cb < HC / 32; ++cb) ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r[cb]);
       ptx::tmem_ld_wait();
-      }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty[acc]);  // accumulator is in registers: the next MMAs may start
-      if (p.debug & 8) continue;
 #pragma unroll
       for (int pass = 0; pass < HC / PC; ++pass) {
         // lane = row: PC columns -> CH chunks of 8 bf16, chunk j at swizzled slot j ^ (row & (CH-1))
@@ -226,8 +217,14 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int col = pass * PC + j * 8 + 2 * e;
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(alpha * __uint_as_float(r[col >> 5][col & 31]),
-                                                      alpha * __uint_as_float(r[col >> 5][(col & 31) + 1]));
+            float s0 = alpha, s1 = alpha;
+            if (cs) {
+              const int gc = nt * BN + half * HC + col;
+              if (gc < p.N) s0 = __fmul_rn(alpha, __ldg(cs + gc));
+              if (gc + 1 < p.N) s1 = __fmul_rn(alpha, __ldg(cs + gc + 1));
+            }
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(s0 * __uint_as_float(r[col >> 5][col & 31]),
+                                                      s1 * __uint_as_float(r[col >> 5][(col & 31) + 1]));
             o[e] = *reinterpret_cast<uint32_t *>(&h2);
           }
           *reinterpret_cast<uint4 *>(wst + lane * RB + ((j ^ (lane & (CH - 1))) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -241,7 +238,7 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
           const int grow = mt * kBM + q * 32 + rr;
           if (grow < p.M && gcol < p.N) {
-            __nv_bfloat16 *dst = p.d + (size_t)grow * p.N + gcol;
+            __nv_bfloat16 *dst = p.d + (size_t)grow * p.ldd + gcol;
             if (vec_ok && gcol + 8 <= p.N) {
               *reinterpret_cast<uint4 *>(dst) = v;
             } else {
@@ -350,11 +347,8 @@ template <int BN, int STAGES, int PC>
 static int launch_gemm(const void *a, const void *b, GemmParams p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, STAGES, PC>;
   auto kern = gemm_nvfp4_kernel<BN, STAGES, PC>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
-  }
+  static SmemAttrCache attr_cache = {};  // per instantiation, per device
+  if (int rc = ensure_dynamic_smem(kern, Cfg::SMEM_BYTES, attr_cache)) return rc;
   CUtensorMap ta, tb;
   if (int rc = cached_operand_map(&ta, a, p.M, p.K / 2, kBM)) return rc;
   if (int rc = cached_operand_map(&tb, b, p.N, p.K / 2, BN)) return rc;
@@ -375,16 +369,16 @@ static int launch_gemm(const void *a, const void *b, GemmParams p, cudaStream_t 
 using namespace arcq;
 
 namespace arcq {
-int launch_gemm_cluster(int shape, const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K,
-                        float alpha, const float *alpha_dev, void *d, cudaStream_t stream);
 int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                     const float *alpha_dev, void *d, cudaStream_t stream);
+                     const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream);
+int launch_gemm_splitk(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
+                       const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, int splits, cudaStream_t stream);
+int splitk_choice(int M, int N, int K);  // 0 = do not split
 }
-static const int kDefaultPair = 1;  // cta_group::2 kernel for shapes with at least one 256x256 tile per SM pair
-static const int kDefaultClusterShape = 0;  // set once the cluster kernel is validated on hardware
 
-extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
-                               int64_t K, float alpha, const float *alpha_dev, void *d, void *stream) {
+extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
+                                  int64_t K, float alpha, const float *alpha_dev, const float *col_scale_dev, int epilogue,
+                                  void *d, int64_t ldd, void *stream) {
   if (!a || !b || !sfa || !sfb || !d) { set_error("null pointer argument"); return ARCQ_EINVAL; }
   if (M < 0 || N < 0 || M > 0x7fffff00 || N > 0x7fffff00) { set_error("M/N out of range"); return ARCQ_EINVAL; }
   if (K <= 0 || K % 64 || K > (1 << 20)) { set_error("K=%lld must be a positive multiple of 64", (long long)K); return ARCQ_EINVAL; }
@@ -392,30 +386,39 @@ extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, co
     set_error("pointers must be 16-byte aligned");
     return ARCQ_EINVAL;
   }
+  if (epilogue != ARCQ_EPILOGUE_NONE && epilogue != ARCQ_EPILOGUE_SWIGLU) { set_error("unknown epilogue %d", epilogue); return ARCQ_EINVAL; }
+  const bool swiglu = epilogue == ARCQ_EPILOGUE_SWIGLU;
+  if (swiglu && N % 256) { set_error("the SwiGLU epilogue needs N %% 256 == 0 (128-row gate/up interleave), got N=%lld", (long long)N); return ARCQ_EINVAL; }
+  const int64_t out_cols = swiglu ? N / 2 : N;
+  if (ldd == 0) ldd = out_cols;
+  if (ldd < out_cols) { set_error("ldd=%lld smaller than the %lld output columns", (long long)ldd, (long long)out_cols); return ARCQ_EINVAL; }
   if (M == 0 || N == 0) return ARCQ_OK;
-  GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, alpha, (int)M, (int)N, (int)K, 0, 0, 0};
-  if (const char *dbg = getenv("ARCQ_GEMM_DEBUG")) p.debug = atoi(dbg);
   cudaStream_t st = (cudaStream_t)stream;
-  // ARCQ_GEMM_CLUSTER=<10*CM+CN> forces a multicast cluster shape (0 = never), ARCQ_GEMM_BN forces the tile
-  // width of the non-cluster kernel; both are for experiments, the defaults below are the tuned choice.
-  const char *ep = getenv("ARCQ_GEMM_PAIR");
+  const Options &o = options();
+  const int sms = sm_count();
+  if (sms <= 0) return ARCQ_ECUDA;
+  if (swiglu) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, 1, d, ldd, st);
+  // small M: weight-streaming bound; split K over a thread-block cluster so every SM pulls on HBM (gemm_splitk.cu)
+  const int splits = o.gemm_splitk >= 0 ? o.gemm_splitk : splitk_choice((int)M, (int)N, (int)K);
+  if (splits >= 2 && M <= 128)
+    return launch_gemm_splitk(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, d, ldd, splits, st);
+  // cta_group::2 kernel for shapes with at least one 256 x 256 tile per SM pair
   const int64_t ptiles = ((M + 255) / 256) * ((N + 255) / 256);
-  const int use_pair = ep ? atoi(ep) : (kDefaultPair && ptiles >= sm_count() / 2);
-  if (use_pair) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, d, st);
-  const char *ec = getenv("ARCQ_GEMM_CLUSTER");
-  int cshape = ec ? atoi(ec) : -1;
+  const bool use_pair = o.gemm_pair >= 0 ? o.gemm_pair != 0 : ptiles >= sms / 2;
+  if (use_pair) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, 0, d, ldd, st);
+  GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, col_scale_dev, alpha,
+               (int)M, (int)N, (int)K, ldd, 0, 0};
   const int64_t tiles256 = ((M + kBM - 1) / kBM) * ((N + 255) / 256);
-  if (cshape < 0) cshape = tiles256 >= 2 * (int64_t)sm_count() ? kDefaultClusterShape : 0;
-  if (cshape > 0)
-    return launch_gemm_cluster(cshape, a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, d, st);
-  const char *e = getenv("ARCQ_GEMM_BN");
-  int bn = e ? atoi(e) : 0;
+  int bn = o.gemm_bn;
   if (bn != 128 && bn != 256) {
     // wide tiles halve A re-reads and MMA issue count; narrow tiles fill the SMs for small problems
-    bn = (tiles256 >= 2 * (int64_t)sm_count() || N % 256 == 0) && N > 128 ? 256 : 128;
+    bn = (tiles256 >= 2 * (int64_t)sms || N % 256 == 0) && N > 128 ? 256 : 128;
   }
-  const char *es = getenv("ARCQ_GEMM_STAGES");
-  const int stages = es ? atoi(es) : 4;
-  if (bn == 256) return stages == 3 ? launch_gemm<256, 3, 64>(a, b, p, st) : launch_gemm<256, 4, 16>(a, b, p, st);
+  if (bn == 256) return launch_gemm<256, 4, 16>(a, b, p, st);
   return launch_gemm<128, 5, 64>(a, b, p, st);
+}
+
+extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
+                               int64_t K, float alpha, const float *alpha_dev, void *d, void *stream) {
+  return arcq_gemm_nvfp4_ex(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, nullptr, ARCQ_EPILOGUE_NONE, d, N, stream);
 }

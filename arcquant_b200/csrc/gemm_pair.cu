@@ -20,6 +20,7 @@
 
 // per-role cycle counters (scripts/gemm_prof.py): build with -DARCQ_GEMM_PROFILE, run with ARCQ_GEMM_PROF=1
 #ifdef ARCQ_GEMM_PROFILE
+#include <stdlib.h>
 #define PROF(...) __VA_ARGS__
 #else
 #define PROF(...)
@@ -54,14 +55,26 @@ struct PCfg {
 struct PParams {
   __nv_bfloat16 *d;
   const float *alpha_dev;
+  const float *col_scale;   // nullable fp32 [N]: column n is scaled by RN(alpha * col_scale[n]) (fused q/k/v, gate/up launches)
   float alpha;
   int M, N, K;
+  int64_t ldd;              // row stride of d in elements
   int ptiles_m, ptiles_n;   // 256 x 256 pair tiles
-  int debug;                // experiments: bit0 skip loads, bit1 skip MMA, bit2 skip UTCCP, bit3 skip stores
-  long long *prof;          // experiments: per-role cycle counters of block 0/1 (nullable)
+  long long *prof;          // -DARCQ_GEMM_PROFILE builds: per-role cycle counters of block 0/1 (nullable)
 };
 
-template <int STAGES>
+// bf16(silu(g)) * u exactly as torch computes `F.silu(g) * u` on bf16 tensors: silu in fp32 (x / (1 + exp(-x)), IEEE
+// division, libdevice expf), rounded to bf16, then an fp32 multiply rounded to bf16
+__device__ __forceinline__ float swiglu_bf16(float g, float u) {
+  const float gb = __bfloat162float(__float2bfloat16_rn(g)), ub = __bfloat162float(__float2bfloat16_rn(u));
+  const float s = __bfloat162float(__float2bfloat16_rn(__fdiv_rn(gb, 1.0f + expf(-gb))));
+  return __fmul_rn(s, ub);
+}
+
+// SWIGLU: the 256 columns of a pair tile are 128 "gate" columns followed by the 128 "up" columns of the SAME 128
+// channels (the fused gate/up weight is interleaved in 128-row blocks, which are whole scale-factor blocks); the
+// epilogue writes d[M, N/2] = bf16(silu(gate)) * up and the [M, N] intermediate never reaches HBM.
+template <int STAGES, bool SWIGLU>
 __global__ void __launch_bounds__(kThreadsP, 1)
 gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                        const __grid_constant__ CUtensorMap tmap_sfa, const __grid_constant__ CUtensorMap tmap_sfb,
@@ -192,12 +205,17 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     }
   } else {
     // ===================== epilogue (warps 2..9 of both CTAs) =====================
+    // plain: warp (q, half) owns lanes [32 q, +32) x columns [128 half, +128).  SWIGLU: gate columns [64 half, +64) and the
+    // matching up columns [128 + 64 half, +64), so one thread holds g and u of the same (row, channel).
     constexpr int HC = kBN / 2, CH = kPC / 8, RB = kPC * 2;
+    constexpr int OUTC = SWIGLU ? HC / 2 : HC;     // output columns per warp
     const int q = warp & 3, half = (warp - 2) >> 2;
     float alpha = p.alpha;
     if (p.alpha_dev) alpha = __ldg(p.alpha_dev);
+    const float *cs = p.col_scale;
     uint8_t *wst = epi + (warp - 2) * Cfg::EPI_WARP_BYTES;
-    const bool vec_ok = (p.N % 8) == 0;
+    const int ncols_out = SWIGLU ? p.N / 2 : p.N;
+    const bool vec_ok = (ncols_out % 8) == 0 && (p.ldd % 8) == 0;
     const uint32_t tempty_leader = ptx::mapa(tempty, 0);
     uint32_t tile_it = 0;
     PROF(long long ew = 0, eld = 0, et0 = clock64();)
@@ -207,47 +225,72 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       ptx::mbar_wait(tfull, tile_it & 1);
       PROF(long long e1 = clock64(); ew += e1 - e0;)
       ptx::tc_fence_after();
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + half * HC;
+      const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
       uint32_t r[HC / 32][32];
 #pragma unroll
-      for (int cb = 0; cb < HC / 32; ++cb) ptx::tmem_ld_32x32b_x32(t_row + cb * 32, r[cb]);
+      for (int cb = 0; cb < HC / 32; ++cb) {
+        const int col = SWIGLU ? (cb >> 1) * HC + half * (HC / 2) + (cb & 1) * 32 : half * HC + cb * 32;
+        ptx::tmem_ld_32x32b_x32(t_lane + col, r[cb]);
+      }
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader);
       PROF(eld += clock64() - e1;)
       const int row_base = (pm * 2 + (int)rank) * kRows + q * 32;
+      // first tile column of this warp's register block cb (input columns of the GEMM, for the per-column scales)
+      const int in_col0 = pn * kBN + (SWIGLU ? half * (HC / 2) : half * HC);
+      const int out_col0 = SWIGLU ? pn * (kBN / 2) + half * (HC / 2) : in_col0;
 #pragma unroll
-      for (int pass = 0; pass < HC / kPC; ++pass) {
+      for (int pass = 0; pass < OUTC / kPC; ++pass) {
 #pragma unroll
         for (int j = 0; j < CH; ++j) {
           uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            const int col = pass * kPC + j * 8 + 2 * e;
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(alpha * __uint_as_float(r[col >> 5][col & 31]),
-                                                      alpha * __uint_as_float(r[col >> 5][(col & 31) + 1]));
+            const int col = pass * kPC + j * 8 + 2 * e;   // column inside this warp's output block
+            float v0, v1;
+            if constexpr (SWIGLU) {
+              float sg0 = alpha, sg1 = alpha, su0 = alpha, su1 = alpha;
+              if (cs) {
+                const int gc = in_col0 + col;
+                if (gc + 1 < p.N) { sg0 = __fmul_rn(alpha, __ldg(cs + gc)); sg1 = __fmul_rn(alpha, __ldg(cs + gc + 1)); }
+                if (gc + HC + 1 < p.N) { su0 = __fmul_rn(alpha, __ldg(cs + gc + HC)); su1 = __fmul_rn(alpha, __ldg(cs + gc + HC + 1)); }
+              }
+              v0 = swiglu_bf16(sg0 * __uint_as_float(r[col >> 5][col & 31]), su0 * __uint_as_float(r[2 + (col >> 5)][col & 31]));
+              v1 = swiglu_bf16(sg1 * __uint_as_float(r[col >> 5][(col & 31) + 1]), su1 * __uint_as_float(r[2 + (col >> 5)][(col & 31) + 1]));
+            } else {
+              float s0 = alpha, s1 = alpha;
+              if (cs) {
+                const int gc = in_col0 + col;
+                if (gc < p.N) s0 = __fmul_rn(alpha, __ldg(cs + gc));
+                if (gc + 1 < p.N) s1 = __fmul_rn(alpha, __ldg(cs + gc + 1));
+              }
+              v0 = s0 * __uint_as_float(r[col >> 5][col & 31]);
+              v1 = s1 * __uint_as_float(r[col >> 5][(col & 31) + 1]);
+            }
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v0, v1);
             o[e] = *reinterpret_cast<uint32_t *>(&h2);
           }
           *reinterpret_cast<uint4 *>(wst + lane * RB + ((j ^ (lane & (CH - 1))) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
         }
         __syncwarp();
         const int j = lane & (CH - 1);
-        const int gcol = pn * kBN + half * HC + pass * kPC + j * 8;
+        const int gcol = out_col0 + pass * kPC + j * 8;
 #pragma unroll
         for (int i = 0; i < CH; ++i) {
           const int rr = i * (32 / CH) + lane / CH;
           const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
           const int grow = row_base + rr;
-          if (grow < p.M && gcol < p.N) {
-            __nv_bfloat16 *dst = p.d + (size_t)grow * p.N + gcol;
-            if (vec_ok && gcol + 8 <= p.N) {
+          if (grow < p.M && gcol < ncols_out) {
+            __nv_bfloat16 *dst = p.d + (size_t)grow * p.ldd + gcol;
+            if (vec_ok && gcol + 8 <= ncols_out) {
               *reinterpret_cast<uint4 *>(dst) = v;
             } else {
               const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
               for (int e = 0; e < 8; ++e)
-                if (gcol + e < p.N) dst[e] = __ushort_as_bfloat16((unsigned short)(w[e >> 1] >> (16 * (e & 1))));
+                if (gcol + e < ncols_out) dst[e] = __ushort_as_bfloat16((unsigned short)(w[e >> 1] >> (16 * (e & 1))));
             }
           }
         }
@@ -265,12 +308,14 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 
 }  // namespace
 
-int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                     const float *alpha_dev, void *d, cudaStream_t stream) {
+template <bool SWIGLU>
+static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
+                              const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, cudaStream_t stream) {
   constexpr int STAGES = 5;
   using Cfg = PCfg<STAGES>;
-  auto kern = gemm_nvfp4_pair_kernel<STAGES>;
-  static int max_pairs = -1;
+  auto kern = gemm_nvfp4_pair_kernel<STAGES, SWIGLU>;
+  static SmemAttrCache attr_cache = {};
+  static int max_pairs[kMaxDevices] = {0};   // co-resident CTA pairs, per device
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -282,19 +327,24 @@ int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *
   cfg.stream = stream;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  if (max_pairs < 0) {
-    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    cfg.gridDim = dim3(2 * 74);
+  if (int rc = ensure_dynamic_smem(kern, Cfg::SMEM_BYTES, attr_cache)) return rc;
+  const int dev = current_device();
+  if (dev < 0) return ARCQ_ECUDA;
+  if (max_pairs[dev] == 0) {
+    const int sms = sm_count();
+    if (sms <= 0) return ARCQ_ECUDA;
+    cfg.gridDim = dim3(2 * (sms / 2));
     int n = 0;
     ARCQ_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
     if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
-    max_pairs = n;
+    max_pairs[dev] = n;
   }
-  PParams p{(__nv_bfloat16 *)d, alpha_dev, alpha, M, N, K, (M + 255) / 256, (N + 255) / 256, 0, nullptr};
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr};
+#ifdef ARCQ_GEMM_PROFILE
   static long long *prof_buf = nullptr;
   const bool do_prof = getenv("ARCQ_GEMM_PROF") != nullptr;
   if (do_prof) { if (!prof_buf) cudaMalloc(&prof_buf, 64 * 8); cudaMemsetAsync(prof_buf, 0, 64 * 8, stream); p.prof = prof_buf; }
-  if (const char *dbg = getenv("ARCQ_GEMM_DEBUG")) p.debug = atoi(dbg);
+#endif
   const int64_t kc = K / 64;
   CUtensorMap ta, tb, tsa, tsb;
   if (int rc = cached_operand_map(&ta, a, M, K / 2, kRows)) return rc;
@@ -302,10 +352,11 @@ int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *
   if (int rc = cached_sf_map(&tsa, sfa, (int64_t)((M + 127) / 128) * kc)) return rc;
   if (int rc = cached_sf_map(&tsb, sfb, (int64_t)((N + 127) / 128) * kc)) return rc;
   int pairs = p.ptiles_m * p.ptiles_n;
-  if (pairs > max_pairs) pairs = max_pairs;
+  if (pairs > max_pairs[dev]) pairs = max_pairs[dev];
   cfg.gridDim = dim3(2 * pairs);
   ARCQ_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, ta, tb, tsa, tsb, p));
   count_launch();
+#ifdef ARCQ_GEMM_PROFILE
   if (do_prof) {
     long long h[64];
     cudaStreamSynchronize(stream);
@@ -316,7 +367,14 @@ int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *
             h[4], h[5], h[6], h[8], h[7], h[9]);
     fprintf(stderr, "[prof] epilogue warp2: total %lld clk, wait-tfull %lld clk, tmem-ld+release %lld clk\n", h[10], h[11], h[12]);
   }
+#endif
   return ARCQ_OK;
+}
+
+int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
+                     const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream) {
+  if (swiglu) return launch_gemm_pair_t<true>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream);
+  return launch_gemm_pair_t<false>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream);
 }
 
 }  // namespace arcq

@@ -248,19 +248,11 @@ static int launch_quant(const QuantParams &p0, cudaStream_t stream) {
   QuantParams p = p0;
   auto kern = quant_kernel<R, FLAVOUR, IS_W, RMS>;
   const size_t smem = quant_smem_bytes(R, p.KQ, p.KE, RMS);
-  static size_t smem_set = 0;  // per instantiation
-  static int occ_cached = 0;
-  if (smem > smem_set) {
-    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
-    occ_cached = 0;
-  }
-  int occ = occ_cached;
-  if (occ == 0 || true) {
-    ARCQ_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
-    if (occ < 1) { set_error("quantise kernel does not fit on an SM (smem %zu B)", smem); return ARCQ_ENOSUP; }
-    occ_cached = occ;
-  }
+  static SmemAttrCache attr_cache = {};  // per instantiation, per device
+  if (int rc = ensure_dynamic_smem(kern, (int)smem, attr_cache)) return rc;
+  int occ = 0;  // fallback kernel for unusual shapes: the occupancy query (host-only, ~1 us) is not worth caching per device
+  ARCQ_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, smem));
+  if (occ < 1) { set_error("quantise kernel does not fit on an SM (smem %zu B)", smem); return ARCQ_ENOSUP; }
   const int sms = sm_count();
   if (sms <= 0) return ARCQ_ECUDA;
   p.num_tiles = (int)(((int64_t)p.M + 127) / 128) * (128 / R);
@@ -295,22 +287,14 @@ static int check_common(const void *x, int64_t M, int KQ, const void *idx, int K
   return ARCQ_OK;
 }
 
-// ARCQ_QUANT_V=1 forces the single-role kernel of this file (experiments); default is the warp-specialised family
-static int quant_version() {
-  static const int v = getenv("ARCQ_QUANT_V") ? atoi(getenv("ARCQ_QUANT_V")) : 3;
-  return v;
-}
-static bool use_ws() { return quant_version() == 2; }
-static bool use_tma() { return quant_version() == 3; }
+// arcq_set_option("quant_family", "1") forces the single-role kernel of this file (its parity tests); default is the
+// TMA-staged family, which hands the shapes it does not take (ARCQ_ENOSUP) to this one
+static bool use_tma() { return options().quant_family == 3; }
 
 template <bool IS_W>
 static int dispatch_quant(const QuantParams &p, int flavour, cudaStream_t st) {
   if (use_tma()) {
     const int rc = launch_quant_tma(p, flavour, IS_W, false, st);
-    if (rc != ARCQ_ENOSUP) return rc;
-  }
-  if (use_ws()) {
-    const int rc = launch_quant_ws(p, flavour, IS_W, false, st);
     if (rc != ARCQ_ENOSUP) return rc;
   }
   const int R = pick_rows(p.KQ, p.KE, false);
@@ -351,8 +335,68 @@ extern "C" int arcq_quantize_x(const void *x, int64_t M, int KQ, const int16_t *
   flavour = resolve_flavour(flavour, KQ);
   if (int rc = check_common(x, M, KQ, idx, KE, flavour, qx, sfx)) return rc;
   if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, 0.0f, (int)M, KQ, KE, 0, 0};
+  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, 0, 0.0f, (int)M, KQ, KE, 0, 0};
   return dispatch_quant<false>(p, flavour, (cudaStream_t)stream);
+}
+
+// ---- fused per-tensor pre-scale (reference callers model/qLlamaLayer.py:73-77) ----------------------
+
+namespace arcq {
+// max |x| over n bf16 elements as the fp32 value of the winning element; non-negative floats order like their bit patterns
+__global__ void __launch_bounds__(256) absmax_kernel(const uint4 *__restrict__ x, int64_t n8, const uint16_t *tail, int ntail,
+                                                      unsigned int *out_bits) {
+  uint32_t m = 0;  // per-halfword running maximum of |bits|
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 v = __ldg(x + i);
+    m = __vmaxu2(m, v.x & 0x7fff7fffu);
+    m = __vmaxu2(m, v.y & 0x7fff7fffu);
+    m = __vmaxu2(m, v.z & 0x7fff7fffu);
+    m = __vmaxu2(m, v.w & 0x7fff7fffu);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < ntail) m = __vmaxu2(m, (uint32_t)(tail[threadIdx.x] & 0x7fffu));
+  uint32_t h = max(m & 0xffffu, m >> 16);
+  h = __reduce_max_sync(0xffffffffu, h);
+  __shared__ uint32_t wmax[8];
+  if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = h;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) h = max(h, wmax[w]);
+    if (h) atomicMax(out_bits, h << 16);
+  }
+}
+}  // namespace arcq
+
+extern "C" int arcq_absmax(const void *x, int64_t n, float *amax_out, void *stream) {
+  if (!amax_out || (n > 0 && !x) || n < 0) { set_error("arcq_absmax: bad argument"); return ARCQ_EINVAL; }
+  if ((uintptr_t)x & 15) { set_error("arcq_absmax: x must be 16-byte aligned"); return ARCQ_EINVAL; }
+  cudaStream_t st = (cudaStream_t)stream;
+  ARCQ_CUDA_TRY(cudaMemsetAsync(amax_out, 0, sizeof(float), st));
+  if (n == 0) return ARCQ_OK;
+  const int sms = sm_count();
+  if (sms <= 0) return ARCQ_ECUDA;
+  const int64_t n8 = n / 8;
+  int64_t blocks = (n8 + 255) / 256;
+  if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
+  if (blocks < 1) blocks = 1;
+  absmax_kernel<<<(int)blocks, 256, 0, st>>>((const uint4 *)x, n8, (const uint16_t *)x + n8 * 8, (int)(n - n8 * 8),
+                                             (unsigned int *)amax_out);
+  ARCQ_CUDA_TRY(cudaGetLastError());
+  count_launch();
+  return ARCQ_OK;
+}
+
+extern "C" int arcq_quantize_x_scaled(const void *x, int64_t M, int KQ, const int16_t *idx, int KE, int flavour,
+                                      const float *amax_dev, int prescale_mode, void *qx, void *sfx, float *scale_out,
+                                      void *stream) {
+  flavour = resolve_flavour(flavour, KQ);
+  if (int rc = check_common(x, M, KQ, idx, KE, flavour, qx, sfx)) return rc;
+  if (!amax_dev) { set_error("arcq_quantize_x_scaled: amax_dev is null"); return ARCQ_EINVAL; }
+  if (prescale_mode != ARCQ_PRESCALE_FP32 && prescale_mode != ARCQ_PRESCALE_BF16_DIVISOR) { set_error("arcq_quantize_x_scaled: unknown prescale_mode %d", prescale_mode); return ARCQ_EINVAL; }
+  if (M == 0) return ARCQ_OK;
+  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, amax_dev, scale_out, prescale_mode, 0.0f, (int)M, KQ, KE, 0, 0};
+  const int rc = launch_quant_tma(p, flavour, false, false, (cudaStream_t)stream);
+  if (rc == ARCQ_ENOSUP) set_error("arcq_quantize_x_scaled: KQ=%d KE=%d is outside the TMA-staged kernel's shapes; pre-scale separately", KQ, KE);
+  return rc;
 }
 
 extern "C" int arcq_quantize_w(const void *w, int64_t N, int KQ, const int16_t *idx, int KE, int flavour, void *qw,
@@ -360,7 +404,7 @@ extern "C" int arcq_quantize_w(const void *w, int64_t N, int KQ, const int16_t *
   flavour = resolve_flavour(flavour, KQ);
   if (int rc = check_common(w, N, KQ, idx, KE, flavour, qw, sfw)) return rc;
   if (N == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)w, idx, nullptr, (uint8_t *)qw, (uint8_t *)sfw, 0.0f, (int)N, KQ, KE, 0, 0};
+  QuantParams p{(const uint16_t *)w, idx, nullptr, (uint8_t *)qw, (uint8_t *)sfw, nullptr, nullptr, 0, 0.0f, (int)N, KQ, KE, 0, 0};
   return dispatch_quant<true>(p, flavour, (cudaStream_t)stream);
 }
 
@@ -373,14 +417,10 @@ extern "C" int arcq_rmsnorm_quantize_x(const void *x, const void *w, float eps, 
     return ARCQ_ENOSUP;
   }
   if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, eps, (int)M, H, KE, 0, 0};
+  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, 0, eps, (int)M, H, KE, 0, 0};
   cudaStream_t st = (cudaStream_t)stream;
   if (use_tma()) {
     const int rc = launch_quant_tma(p, ARCQ_FLAVOUR_16, false, true, st);
-    if (rc != ARCQ_ENOSUP) return rc;
-  }
-  if (use_ws()) {
-    const int rc = launch_quant_ws(p, ARCQ_FLAVOUR_16, false, true, st);
     if (rc != ARCQ_ENOSUP) return rc;
   }
   switch (pick_rows(H, KE, true)) {

@@ -1,4 +1,4 @@
-// quant.cuh -- parameters shared by the quantise kernel families (quant.cu, quant_ws.cu).
+// quant.cuh -- parameters shared by the quantise kernel families (quant.cu, quant_tma.cu).
 #pragma once
 #include "common.cuh"
 
@@ -10,10 +10,13 @@ struct QuantParams {
   const uint16_t *w;     // rmsnorm weight bf16 [KQ] (RMS only)
   uint8_t *q;            // [M, K/2]
   uint8_t *sf;           // swizzled scale bytes
+  const float *amax;     // PRESCALE only: device fp32 max|x| of the whole tensor (arcq_absmax)
+  float *scale_out;      // PRESCALE only (nullable): receives amax / 2688, the per-tensor scale the GEMM alpha needs
+  int prescale_mode;     // PRESCALE only: ARCQ_PRESCALE_FP32 / ARCQ_PRESCALE_BF16_DIVISOR
   float eps;
   int M, KQ, KE;
   int num_tiles;
-  int debug;  // experiment bits (ARCQ_QUANT_DEBUG): 1 skip transpose, 2 skip gather, 4 skip quantise math, 8 skip residuals
+  int debug;  // -DARCQ_EXPERIMENT builds only: 1 skip transpose, 2 skip gather, 4 skip quantise math, 8 skip residuals
 };
 
 constexpr float kFp4Max = 6.0f;            // reorder.cu:17
@@ -58,9 +61,7 @@ template <int R> __device__ __forceinline__ int chan_pos_m(int c) {
 // bytes added to every staged row so that the 8 row addresses of one ldmatrix fall into 8 different 16-byte bank groups
 __host__ __device__ constexpr int stage_pad(int R) { return R == 8 ? 16 : R == 4 ? 32 : R == 2 ? 64 : 0; }
 
-// warp-specialised kernel family (quant_ws.cu); returns ARCQ_ENOSUP for shapes it does not take
-// TMA-staged kernel family (quant_tma.cu); same contract
+// TMA-staged kernel family (quant_tma.cu); returns ARCQ_ENOSUP for shapes it does not take
 int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);
-int launch_quant_ws(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);
 
 }  // namespace arcq

@@ -75,6 +75,51 @@ static __device__ __forceinline__ void fsqacc2(float &c0, float &c1, float a0, f
   asm("mov.b64 {%0, %1}, %2;" : "=f"(c0), "=f"(c1) : "l"(c));
 }
 
+// (a0*b0 + c0, a1*b1 + c1) with one packed FFMA2
+static __device__ __forceinline__ void ffma2(float &d0, float &d1, float a0, float a1, float b0, float b1, float c0, float c1) {
+  uint64_t a, b, c, d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(b) : "f"(b0), "f"(b1));
+  asm("mov.b64 %0, {%1, %2};" : "=l"(c) : "f"(c0), "f"(c1));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(d0), "=f"(d1) : "l"(d));
+}
+
+// Per-tensor pre-scale of the reference callers, fused (model/qLlamaLayer.py:73-77: `x / scale` on a bf16 tensor with a
+// 0-dim fp32 scale = fp32 IEEE division, then bf16 RNE).  v = bf16x2 of two elements; returns bf16x2 of the two quotients.
+// Fast path: q0 = x * RN(1/scale); r = fma(-scale, q0, x) (exact); q = fma(r, RN(1/scale), q0) is the correctly rounded
+// fp32 quotient (Markstein) whenever the remainder does not underflow (|x| >= 2^-100) and the significand of scale is not
+// all ones; PrescaleCtx::slow covers those scales, and quotients of |x| < 2^-100 (only possible error: a last-place
+// difference of a value below 2^-48 of the tensor maximum) quantise to code +-0 with the sign forced below -- unobservable.
+struct PrescaleCtx { float scale, rcp; bool slow; };
+// bf16_divisor: torch's CUDA TensorIterator casts a 0-dim CUDA fp32 divisor to the common dtype (bf16) before the fp32
+// division (BinaryFunctor<scalar_t, scalar_t, ...>); a 1-element 1-D divisor, a Python float or the CPU path divide by
+// the fp32 value.  The caller says which expression it replaces (ARCQ_PRESCALE_* in include/arcq.h).
+static __device__ __forceinline__ PrescaleCtx make_prescale(float amax, bool bf16_divisor, float &scale_fp32) {
+  PrescaleCtx c;
+  scale_fp32 = __fdiv_rn(amax, 2688.0f);  // torch.max(x.abs()).float() / (448.0 * 6.0)
+  c.scale = bf16_divisor ? __bfloat162float(__float2bfloat16_rn(scale_fp32)) : scale_fp32;
+  c.rcp = __frcp_rn(c.scale);
+  c.slow = !(amax >= 9.094947017729282e-13f && amax <= 1.152921504606847e18f) || (__float_as_uint(c.scale) & 0x7fffffu) == 0x7fffffu;
+  return c;
+}
+static __device__ __forceinline__ uint32_t prescale_bf16x2(uint32_t v, const PrescaleCtx &c) {
+  const float a = bf16lo_to_f32(v), b = bf16hi_to_f32(v);
+  float qa, qb;
+  if (c.slow) {
+    qa = __fdiv_rn(a, c.scale);
+    qb = __fdiv_rn(b, c.scale);
+  } else {
+    float ra, rb;
+    fmul2(qa, qb, a, b, c.rcp, c.rcp);
+    ffma2(ra, rb, qa, qb, -c.scale, -c.scale, a, b);
+    ffma2(qa, qb, ra, rb, c.rcp, c.rcp, qa, qb);
+  }
+  uint32_t o;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(o) : "f"(qb), "f"(qa));
+  return (o & 0x7fff7fffu) | (v & 0x80008000u);  // the quotient has the sign of x (scale > 0), zeros included
+}
+
 // rmsnorm of two rows at once (rmsnorm.cu:165-171): v[i] = bf16x2 {row a, row b} of element i -> bf16((x * w) * rstd)
 static __device__ __forceinline__ void normalise16x2(uint32_t (&v)[16], const float (&wf)[16], float rstd_a, float rstd_b) {
 #pragma unroll

@@ -16,7 +16,15 @@
 #include "quant.cuh"
 #include "quant_math.cuh"
 #include "ptx.cuh"
+
+// Work-skipping experiment bits exist only in -DARCQ_EXPERIMENT builds (scripts/build_variant.py); the product library
+// compiles them out, so it cannot be made to skip its work.
+#ifdef ARCQ_EXPERIMENT
 #include <stdlib.h>
+#define ARCQ_DBG(p, bit) (((p).debug & (bit)) != 0)
+#else
+#define ARCQ_DBG(p, bit) false
+#endif
 
 namespace arcq {
 namespace {
@@ -47,7 +55,8 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
   return c;
 }
 
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
+// PS: fused per-tensor pre-scale (activations only): every gathered element becomes bf16(x / (amax / 2688)) first
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS>
 __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantParams p, const int S) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int CB = 2 * R;        // bytes of one channel chunk
@@ -187,6 +196,12 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
   uint32_t own_off[OWN ? 16 : 1];
   if constexpr (OWN) load_offsets(tid / RB < ngroups ? tid / RB : 0, own_off);
+  PrescaleCtx psc = {1.0f, 1.0f, false};
+  if constexpr (PS) {
+    float scale_fp32;
+    psc = make_prescale(__ldg(p.amax), p.prescale_mode == ARCQ_PRESCALE_BF16_DIVISOR, scale_fp32);
+    if (p.scale_out && blockIdx.x == 0 && tid == 0) *p.scale_out = scale_fp32;
+  }
 
   // scale bytes of one finished tile leave as contiguous 4R-byte runs of the swizzled layout
   auto copy_out_sf = [&](int buf, int blk, int t) {
@@ -302,7 +317,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           const int b = 4 * k + m;
           return tile_s + (uint32_t)((b * 8 + (r ^ (b & 7))) * 16);
         };
-        const int nch = (p.debug & 1) ? 0 : KQ / CW;
+        const int nch = ARCQ_DBG(p, 1) ? 0 : KQ / CW;
         uint32_t la = ld_addr(warp), sa = st_addr(warp);
 #pragma unroll 4
         for (int k = warp; k < nch; k += NW) {
@@ -313,14 +328,14 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           sa += NW * CW * CB;
         }
         if constexpr (R == 2) {  // KQ = 64 (mod 128): the last half step has two matrices
-          if ((KQ & 64) && warp == nch % NW && !(p.debug & 1)) {
+          if ((KQ & 64) && warp == (KQ / CW) % NW && !ARCQ_DBG(p, 1)) {
             uint32_t f[4];
-            ptx::ldsm_x2_t(ld_addr(nch), f);
-            ptx::stsm_x2(st_addr(nch), f);
+            ptx::ldsm_x2_t(ld_addr(KQ / CW), f);
+            ptx::stsm_x2(st_addr(KQ / CW), f);
           }
         }
       } else {
-        for (int u = tid; u < ((p.debug & 1) ? 0 : nunits); u += THREADS) {
+        for (int u = tid; u < (ARCQ_DBG(p, 1) ? 0 : nunits); u += THREADS) {
           uint4 in[R];
           load_unit(u, in);
           store_unit(u, in);
@@ -362,7 +377,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     for (int item = tid; item < ngroups * RB; item += THREADS) {
       const int g = item / RB, rb = item % RB;
       uint32_t v[16][RTP];
-      if (p.debug & 2) {
+      if (ARCQ_DBG(p, 2)) {
 #pragma unroll
         for (int i = 0; i < 16; ++i)
 #pragma unroll
@@ -375,6 +390,12 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
         load_offsets(g, off);
 #pragma unroll
         for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + off[i] + rb * (2 * RT), v[i]);
+      }
+      if constexpr (PS) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+#pragma unroll
+          for (int w = 0; w < RTP; ++w) v[i][w] = prescale_bf16x2(v[i][w], psc);
       }
       float wf[RMS ? 16 : 1];
       if constexpr (RMS) load_w(g, wf);
@@ -442,7 +463,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           uint32_t c_lo, c_hi;
           float sc;
           uint32_t sfb;
-          if (p.debug & 4) { sfb = __float_as_uint(x[0]) >> 24; c_lo = __float_as_uint(x[1]); c_hi = __float_as_uint(x[15]); sc = x[2]; }
+          if (ARCQ_DBG(p, 4)) { sfb = __float_as_uint(x[0]) >> 24; c_lo = __float_as_uint(x[1]); c_hi = __float_as_uint(x[15]); sc = x[2]; }
           else sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
           uint32_t xb[8];
 #pragma unroll
@@ -457,7 +478,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     if constexpr (!IS_W) {
       __syncthreads();  // stash complete; also: nobody reads the tile any more (the next transpose may overwrite it)
 #ifndef ARCQ_PHASEB_QUAD  // one thread per (group,row) item; the 4-lanes-per-item variant below measured 5 % slower (r1l_quant.log)
-      const int nitems = (p.debug & 8) ? 0 : (KE / 16) * R;
+      const int nitems = ARCQ_DBG(p, 8) ? 0 : (KE / 16) * R;
       for (int item = tid; item < nitems; item += THREADS) {
 #ifdef ARCQ_STASH_LRMAJOR
         const int nper = KE / 16, lr = item / nper, g = G + item % nper;
@@ -481,7 +502,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       }
 #else
       // four lanes share one (group,row) item: each requantises 4 of its 16 residuals, the quad reduces amax
-      const int nitems = (p.debug & 8) ? 0 : (KE / 16) * R;
+      const int nitems = ARCQ_DBG(p, 8) ? 0 : (KE / 16) * R;
       const int sub = lane & 3;
       for (int base = warp * 8; base < nitems; base += (THREADS / 32) * 8) {  // warp-uniform: shuffles below
         const int it0 = base + (lane >> 2);
@@ -534,17 +555,16 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
 constexpr int kSmemPerSm = 227 * 1024;
 
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB>
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS>
 int launch(const QuantParams &p0, int S, cudaStream_t stream) {
   QuantParams p = p0;
+#ifdef ARCQ_EXPERIMENT
   if (const char *e = getenv("ARCQ_QUANT_DEBUG")) p.debug = atoi(e);
-  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB>;
+#endif
+  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB, PS>;
   const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S).total;
-  static int smem_set = 0;  // per instantiation
-  if (smem > smem_set) {
-    ARCQ_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    smem_set = smem;
-  }
+  static SmemAttrCache attr_cache = {};  // per instantiation, per device
+  if (int rc = ensure_dynamic_smem(kern, smem, attr_cache)) return rc;
   const int sms = sm_count();
   if (sms <= 0) return ARCQ_ECUDA;
   p.num_tiles = (int)(((int64_t)p.M + 127) / 128) * (128 / R);
@@ -555,11 +575,11 @@ int launch(const QuantParams &p0, int S, cudaStream_t stream) {
   return ARCQ_OK;
 }
 
-template <int R, int RT, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS>
+template <int R, int RT, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS, bool PS = false>
 int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t st) {
-  if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB>(p, S, st);
-  if (tab32) return launch<R, RT, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB>(p, S, st);
-  return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB>(p, S, st);
+  if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB, PS>(p, S, st);
+  if (tab32) return launch<R, RT, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB, PS>(p, S, st);
+  return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB, PS>(p, S, st);
 }
 
 template <int R, int RT, int THREADS, int MINB>
@@ -567,6 +587,9 @@ int launch_kind(const QuantParams &p, int flavour, bool is_w, bool rms, int S, b
   if (rms) return launch_tab<R, RT, THREADS, MINB, 0, false, true>(p, S, tab32, own, st);
   if (is_w) return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, true, false>(p, S, tab32, own, st)
                                               : launch_tab<R, RT, THREADS, MINB, 0, true, false>(p, S, tab32, own, st);
+  if (p.amax)
+    return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false, true>(p, S, tab32, own, st)
+                                      : launch_tab<R, RT, THREADS, MINB, 0, false, false, true>(p, S, tab32, own, st);
   return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false>(p, S, tab32, own, st)
                                     : launch_tab<R, RT, THREADS, MINB, 0, false, false>(p, S, tab32, own, st);
 }
@@ -590,10 +613,9 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
                        {1, wide, 1, 2, 1}, {1, wide, 1, 1, 1}};
   Cfg c{0, 0, 0, 0, 0};
   bool tab32 = false, own = false;
-  if (const char *e = getenv("ARCQ_QUANT_TMA")) {  // experiment knob: "R,threads,S" (threads 256 = two CTAs per SM)
-    int r = 0, th = 0, s = 0, rt = 0, mb = 0;  // "R,threads,S[,RT,CTAs/SM]"
-    const int nf = sscanf(e, "%d,%d,%d,%d,%d", &r, &th, &s, &rt, &mb);
-    if (nf >= 3) c = Cfg{r, th, nf >= 5 ? mb : (th == 256 ? 2 : 1), s, nf >= 4 ? rt : r};
+  {  // arcq_set_option("quant_tile", "R,threads,S,RT,CTAs/SM"): the parity tests force every tile organisation
+    const int *q = options().quant_tile;
+    if (q[0] > 0) c = Cfg{q[0], q[1], q[4], q[2], q[3]};
   }
   if (c.R == 0) {
     for (const Cfg &k : cands) {
@@ -615,8 +637,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   if (c.R == RR && c.RT == RTT && c.threads == TH && c.minb == MB) \
     return launch_kind<RR, RTT, TH, MB>(p, flavour, is_w, rms, c.S, tab32, own, stream);
   ARCQ_T(4, 4, 256, 2) ARCQ_T(4, 4, 512, 1) ARCQ_T(2, 2, 256, 2) ARCQ_T(2, 2, 512, 1) ARCQ_T(1, 1, 512, 1)
-  ARCQ_T(2, 2, 256, 3) ARCQ_T(2, 2, 256, 4) ARCQ_T(4, 4, 256, 3)  // experiments: more CTAs per SM
-  ARCQ_T(8, 8, 512, 1) ARCQ_T(8, 4, 512, 1)  // not chosen by default: measured within 4 % of the 4-row tile (r1_quant_cfg_sweep.log)
+  ARCQ_T(8, 8, 512, 1) ARCQ_T(8, 4, 512, 1)
 #undef ARCQ_T
   return ARCQ_ENOSUP;
 }

@@ -69,7 +69,11 @@ def _rope(q, k):
 
 
 class ArcDecoderLayer(torch.nn.Module):
-    def __init__(self, cfg: PrefillConfig, dev, gen, world=1, rank=0, group=None, keep_ref=False):
+    """fused=True (default): 4 quantise + 4 GEMM launches per layer -- q/k/v as ONE GEMM over the concatenated weight with
+    per-column scales, gate/up as ONE GEMM whose epilogue writes bf16(silu(gate)) * up, per-tensor pre-scales inside the
+    quantise kernels.  fused=False: the reference's launch structure (7 GEMMs, SiLU*up and the pre-scales in torch)."""
+
+    def __init__(self, cfg: PrefillConfig, dev, gen, world=1, rank=0, group=None, keep_ref=False, fused=True):
         super().__init__()
         from . import agemm
         self.ref = {} if keep_ref else None  # bf16 weights / biases kept only for the parity test
@@ -79,6 +83,7 @@ class ArcDecoderLayer(torch.nn.Module):
             raise ValueError("heads=%d / intermediate=%d do not shard over %d ranks" % (cfg.heads, I, world))
         self.local_heads = cfg.heads // world
         self.head_dim = H // cfg.heads
+        self.fused = bool(fused) and (H // world) % 128 == 0 and (I // world) % 128 == 0
         self.idx_h1, self.idx_h2 = _rand_index(H, dev, gen), _rand_index(H, dev, gen)  # inputs of qkv and of gate/up
         idx_o, idx_d = _rand_index(H, dev, gen), _rand_index(I, dev, gen)
         self.norm1 = torch.ones(H, dtype=torch.bfloat16, device=dev)
@@ -93,8 +98,11 @@ class ArcDecoderLayer(torch.nn.Module):
                 self.ref[name] = (w, b)
             return w
 
+        # rmsnorm_quantize_x is always the 16-wide flavour (bindings.cpp:243): the weights it feeds must be too
+        F16 = agemm.FLAVOUR_16
+
         def col(name, n, k, idx, ke, b=None):
-            return tp.ColumnParallelQLinear(weight(name, n, k, b), idx, ke, world, rank, b)
+            return tp.ColumnParallelQLinear(weight(name, n, k, b), idx, ke, world, rank, b, flavour=F16)
 
         self.q = col("q", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
         self.k = col("k", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
@@ -103,6 +111,14 @@ class ArcDecoderLayer(torch.nn.Module):
         self.up = col("up", I, H, self.idx_h2, cfg.ke_hidden)
         self.o = tp.RowParallelQLinear(weight("o", H, H), idx_o, cfg.ke_hidden, world, rank, group=group)
         self.down = tp.RowParallelQLinear(weight("down", H, I), idx_d, cfg.ke_intermediate, world, rank, group=group)
+        if self.fused:
+            self.qkv_w = agemm.fuse_weights([(l.W, l.scale_w, l.scale) for l in (self.q, self.k, self.v)])
+            self.qkv_bias = torch.cat([l.bias for l in (self.q, self.k, self.v)]) if cfg.qkv_bias else None
+            self.gu_w = agemm.interleave_gate_up((self.gate.W, self.gate.scale_w, self.gate.scale),
+                                                 (self.up.W, self.up.scale_w, self.up.scale))
+            for l in (self.q, self.k, self.v, self.gate, self.up):  # the fused copies are the ones that run
+                l.W = l.scale_w = None
+            self.one = torch.ones(1, dtype=torch.float32, device=dev)
 
     def _norm_linears(self, x2d, w, idx, ke, layers):
         """One fused rmsnorm+quantise launch feeding several column-parallel GEMMs (modeling_arc.py:220-227)."""
@@ -111,18 +127,36 @@ class ArcDecoderLayer(torch.nn.Module):
 
     @torch.no_grad()
     def forward(self, h):
+        ag = self.agemm
         B, S, H = h.shape
         x2d = h.reshape(B * S, H)
-        q, k, v = self._norm_linears(x2d, self.norm1, self.idx_h1, self.cfg.ke_hidden, (self.q, self.k, self.v))
+        if self.fused:
+            qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm1, self.cfg.eps, self.idx_h1, self.cfg.ke_hidden)
+            qkv = ag.matmul(qx, self.qkv_w[0], sfx, self.qkv_w[1], self.one, col_scale=self.qkv_w[2])
+            if self.qkv_bias is not None:
+                qkv = qkv + self.qkv_bias
+            q, k, v = qkv.split(H // self.world, dim=1)
+        else:
+            q, k, v = self._norm_linears(x2d, self.norm1, self.idx_h1, self.cfg.ke_hidden, (self.q, self.k, self.v))
         shp = (B, S, self.local_heads, self.head_dim)
-        q, k, v = (t.view(shp).transpose(1, 2) for t in (q, k, v))
+        q, k, v = (t.reshape(shp).transpose(1, 2) for t in (q, k, v))
         q, k = _rope(q, k)
         a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B * S, -1).contiguous()
-        h = h + self.o(a).view(B, S, H)                       # quantise (local permutation + ARC) -> GEMM -> all-reduce
+        h = h + self._row(self.o, a).view(B, S, H)              # quantise (local permutation + ARC) -> GEMM -> all-reduce
         x2d = h.reshape(B * S, H)
-        g, u = self._norm_linears(x2d, self.norm2, self.idx_h2, self.cfg.ke_hidden, (self.gate, self.up))
-        m = (F.silu(g) * u).contiguous()
-        return h + self.down(m).view(B, S, H)
+        if self.fused:
+            qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm2, self.cfg.eps, self.idx_h2, self.cfg.ke_hidden)
+            m = ag.matmul(qx, self.gu_w[0], sfx, self.gu_w[1], self.one, col_scale=self.gu_w[2], epilogue=ag.EPILOGUE_SWIGLU)
+        else:
+            g, u = self._norm_linears(x2d, self.norm2, self.idx_h2, self.cfg.ke_hidden, (self.gate, self.up))
+            m = (F.silu(g) * u).contiguous()
+        return h + self._row(self.down, m).view(B, S, H)
+
+    def _row(self, layer, x_local):
+        y = layer.forward_quantized(*layer.quantize_input(x_local, fused=self.fused))
+        if self.world > 1:
+            dist.all_reduce(y, op=dist.ReduceOp.SUM, group=self.group)
+        return y
 
 
 def reference_layer_forward(layer: "ArcDecoderLayer", h: torch.Tensor) -> torch.Tensor:
@@ -146,11 +180,12 @@ def reference_layer_forward(layer: "ArcDecoderLayer", h: torch.Tensor) -> torch.
 
 
 class ArcPrefillModel(torch.nn.Module):
-    def __init__(self, cfg: PrefillConfig, device, seed=0, world=1, rank=0, group=None, keep_ref=False):
+    def __init__(self, cfg: PrefillConfig, device, seed=0, world=1, rank=0, group=None, keep_ref=False, fused=True):
         super().__init__()
         gen = torch.Generator(device=device).manual_seed(seed)  # same seed on every rank: shards of the same weights
         self.cfg = cfg
-        self.layers = torch.nn.ModuleList([ArcDecoderLayer(cfg, device, gen, world, rank, group, keep_ref) for _ in range(cfg.layers)])
+        self.layers = torch.nn.ModuleList([ArcDecoderLayer(cfg, device, gen, world, rank, group, keep_ref, fused)
+                                           for _ in range(cfg.layers)])
 
     @torch.no_grad()
     def forward(self, h):

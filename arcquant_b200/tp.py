@@ -65,24 +65,34 @@ def nvfp4_scale(t: torch.Tensor, signed: bool) -> torch.Tensor:
 class QLinearShard(torch.nn.Module):
     """One rank's slice of a QLinearLayer (model/qLinearLayer.py:29-77): quantised weight + per-tensor scale."""
 
-    def __init__(self, weight: torch.Tensor, reorder_index: torch.Tensor, select_num: int, bias=None):
+    def __init__(self, weight: torch.Tensor, reorder_index: torch.Tensor, select_num: int, bias=None, flavour: int = -1):
+        """flavour: ARC interleave / residual formula of BOTH sides of this linear (-1 = the reference's KQ table).
+        Layers fed by ``rmsnorm_quantize_x`` must pass FLAVOUR_16: that entry point is always 16-wide (bindings.cpp:243)
+        while the KQ table picks the 32-wide weight layout for KQ in {3584, 18944, 27648, 28672} (:199) -- the
+        reference's own mismatch, which mis-pairs the ARC columns of X and W whenever KE > 0."""
         super().__init__()
         from . import agemm
         self.agemm = agemm
         self.out_features, self.in_features = weight.shape
         self.select_num = int(select_num)
+        self.flavour = int(flavour)
         self.register_buffer("reorder_index", reorder_index.to(torch.int16).to(weight.device).contiguous())
         scale = nvfp4_scale(weight, signed=True)
         w = (weight / scale).to(torch.bfloat16).contiguous()
-        self.W, self.scale_w = agemm.reorder_quantize_w(w, self.reorder_index, self.select_num)
+        self.W, self.scale_w = agemm.reorder_quantize_w(w, self.reorder_index, self.select_num, self.flavour)
         self.register_buffer("scale", scale.reshape(1))
         self.bias = bias
 
     @torch.no_grad()
-    def quantize_input(self, x: torch.Tensor):
-        """NVFP4_reorder_quantize_x (qLlamaLayer.py:73-77) without the host sync: the scale stays a device scalar."""
+    def quantize_input(self, x: torch.Tensor, fused: bool = True):
+        """NVFP4_reorder_quantize_x (qLlamaLayer.py:73-77) without the host sync: the scale stays a device scalar.
+        fused: max|x| pre-pass + in-kernel `bf16(x / scale)` (two launches, X read twice) instead of torch's abs / max /
+        divide passes in front of the kernel; same bytes (tests/test_gpu_prescale.py)."""
+        if fused and self.in_features % 64 == 0 and self.select_num % 64 == 0:  # shapes of the TMA-staged kernel
+            return self.agemm.reorder_quantize_x_scaled(x, self.reorder_index, self.select_num, self.flavour)
         scale = nvfp4_scale(x, signed=False).reshape(1)
-        qx, scale_x = self.agemm.reorder_quantize_x((x / scale).to(torch.bfloat16), self.reorder_index, self.select_num)
+        qx, scale_x = self.agemm.reorder_quantize_x((x / scale).to(torch.bfloat16), self.reorder_index, self.select_num,
+                                                    self.flavour)
         return qx, scale_x, scale
 
     @torch.no_grad()
@@ -100,20 +110,20 @@ class QLinearShard(torch.nn.Module):
 class ColumnParallelQLinear(QLinearShard):
     """N-split: this rank holds rows [lo, hi) of the weight; input replicated; output is the rank's N/world columns."""
 
-    def __init__(self, weight, reorder_index, select_num, world: int, rank: int, bias=None):
+    def __init__(self, weight, reorder_index, select_num, world: int, rank: int, bias=None, flavour: int = -1):
         lo, hi = split_rows(weight.shape[0], world, rank)
         super().__init__(weight[lo:hi].contiguous(), reorder_index, select_num,
-                         None if bias is None else bias[lo:hi].contiguous())
+                         None if bias is None else bias[lo:hi].contiguous(), flavour)
         self.world, self.rank = world, rank
 
 
 class RowParallelQLinear(QLinearShard):
     """K-split by channel ownership with the ARC residual columns kept on the owning shard; all-reduce of partials."""
 
-    def __init__(self, weight, reorder_index, select_num, world: int, rank: int, bias=None, group=None):
+    def __init__(self, weight, reorder_index, select_num, world: int, rank: int, bias=None, group=None, flavour: int = -1):
         lo, hi = split_rows(weight.shape[1], world, rank, 64)
         local_idx, ke = shard_reorder_index(reorder_index, select_num, world, rank)
-        super().__init__(weight[:, lo:hi].contiguous(), local_idx, ke, bias if rank == 0 else None)
+        super().__init__(weight[:, lo:hi].contiguous(), local_idx, ke, bias if rank == 0 else None, flavour)
         self.world, self.rank, self.group = world, rank, group
         self.k_slice = (lo, hi)
 

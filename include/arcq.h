@@ -75,6 +75,46 @@ int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *s
                     int64_t N, int64_t K, float alpha, const float *alpha_dev, void *d,
                     void *stream);
 
+/* matmul with a fused epilogue and per-column scales -- the same kernels as arcq_gemm_nvfp4 (which is this call with
+ * col_scale_dev = NULL, epilogue = NONE, ldd = N).  SURVEY.md §8 f2/f3; reference call sites that share one quantised
+ * input: model/qLlamaLayer.py:301-303 (q/k/v), :432 (gate/up), benchmarks/modeling_arc.py:109-111,165-167.
+ *   col_scale_dev (nullable) fp32 [N]: column n is scaled by RN(alpha * col_scale_dev[n]) -- several weights, each with
+ *       its own per-tensor scale (qLinearLayer.py:26), concatenated along N (rows a multiple of 128) run as ONE launch;
+ *   epilogue ARCQ_EPILOGUE_SWIGLU: b is the gate and up weights interleaved in 128-row blocks (rows [256j, 256j+128) =
+ *       gate rows [128j, +128), rows [256j+128, 256j+256) = up rows [128j, +128)); d is bf16 [M, N/2] =
+ *       bf16(silu(bf16 gate)) * bf16 up, rounded exactly like torch's `F.silu(g) * u` on bf16 tensors
+ *       (modeling_arc.py:110); N % 256 == 0;
+ *   ldd: row stride of d in elements (0 = dense). */
+#define ARCQ_EPILOGUE_NONE 0
+#define ARCQ_EPILOGUE_SWIGLU 1
+int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M,
+                       int64_t N, int64_t K, float alpha, const float *alpha_dev,
+                       const float *col_scale_dev, int epilogue, void *d, int64_t ldd, void *stream);
+
+/* Fused per-tensor pre-scale of the reference callers (NVFP4_reorder_quantize_x, model/qLlamaLayer.py:73-77,
+ * qQwenLayer.py:72-75, benchmarks/modeling_arc.py:58-61: `scale = max|x| / 2688; agemm.reorder_quantize_x(x / scale)`).
+ *   arcq_absmax: amax_out[0] = max |x| over n bf16 elements, as fp32 (one memset + one kernel, stream ordered);
+ *   arcq_quantize_x_scaled: arcq_quantize_x applied to bf16(x / scale), scale = amax / 2688, computed in-kernel with
+ *       torch-identical rounding (fp32 IEEE division, bf16 RNE); scale_out[0] (nullable) receives the fp32 scale for the
+ *       GEMM alpha.  prescale_mode names the torch expression being replaced:
+ *         ARCQ_PRESCALE_FP32          divisor used as fp32: `(x / scale.reshape(1)).to(bf16)`, CPU tensors, Python floats;
+ *         ARCQ_PRESCALE_BF16_DIVISOR  divisor rounded to bf16 first: `x / scale` with x a bf16 CUDA tensor and scale a
+ *                                     0-dim CUDA fp32 tensor (TensorIterator casts the operand to the common dtype) --
+ *                                     the literal expression of qLlamaLayer.py:76.
+ * Bytes equal "torch pre-scale, then arcq_quantize_x".  ARCQ_ENOSUP for shapes only the fallback kernel takes. */
+#define ARCQ_PRESCALE_FP32 0
+#define ARCQ_PRESCALE_BF16_DIVISOR 1
+int arcq_absmax(const void *x, int64_t n, float *amax_out, void *stream);
+int arcq_quantize_x_scaled(const void *x, int64_t M, int KQ, const int16_t *idx, int KE, int flavour,
+                           const float *amax_dev, int prescale_mode, void *qx, void *sfx, float *scale_out,
+                           void *stream);
+
+/* name = value override of a shape-driven kernel choice ("" = back to the default).  Every choice computes the same
+ * result; the parity tests force each tile organisation through this.  Options: "quant_tile" = "R,threads,S,RT,CTAs/SM",
+ * "quant_family" = 3 | 1, "gemm_pair" = 0 | 1, "gemm_bn" = 128 | 256, "gemm_splitk" = 0 | 2 | 4 | 8.  The product
+ * library reads NO environment variables and has no switch that skips work. */
+int arcq_set_option(const char *name, const char *value);
+
 /* Number of kernels this library has launched since load (all entry points). */
 int64_t arcq_launch_count(void);
 

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--layers", type=int, default=None)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--unfused", action="store_true", help="the reference's launch structure: 7 GEMMs + torch glue per layer")
     args = ap.parse_args()
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -32,7 +33,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     cfg = prefill.PrefillConfig.named(args.model, args.layers)
-    model = prefill.ArcPrefillModel(cfg, dev, world=world, rank=rank)
+    model = prefill.ArcPrefillModel(cfg, dev, world=world, rank=rank, fused=not args.unfused)
     h = torch.randn(args.bsz, args.seq, cfg.hidden, device=dev, generator=torch.Generator(device=dev).manual_seed(1)).to(torch.bfloat16)
     for _ in range(args.warmup):
         model(h)
@@ -58,7 +59,8 @@ def main():
             "gpu_launches_per_forward": (agemm.launch_count() - n0) / args.steps, "data": "synthetic, random-init weights",
             "config": {"workload": "%s decoder stack prefill (speed-model shape, MHA), %d layers" % (args.model, cfg.layers),
                        "bsz": args.bsz, "seq": args.seq, "parallelism": "tp%d" % world if world > 1 else "single GPU",
-                       "attention": "torch SDPA (not on the hot path)"}}))
+                       "attention": "torch SDPA (not on the hot path)",
+                       "launches": "fused q/k/v + SwiGLU-epilogue gate/up + in-kernel pre-scale" if not args.unfused else "reference structure (7 GEMMs per layer)"}}))
     if world > 1:
         dist.destroy_process_group()
 

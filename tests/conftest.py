@@ -27,3 +27,19 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+@pytest.fixture
+def arcq_option():
+    """Force a kernel / tile choice through arcq_set_option for one test (every choice computes the same result);
+    restores the shape-driven defaults afterwards."""
+    from arcquant_b200 import agemm
+    touched = []
+
+    def set_(name, value):
+        agemm.set_option(name, str(value))
+        touched.append(name)
+
+    yield set_
+    for name in touched:
+        agemm.set_option(name, "")

@@ -74,6 +74,24 @@ def fakequant():
         out[tag + "_w"] = w.numpy()
         out[tag + "_qw"] = qw.numpy().astype(np.float32)
         out[tag + "_sw"] = np.float32(float(sw))
+    # a REAL permutation (ascending-absmax argsort of un-sorted channels, utilize.py:42): pins the
+    # `topk = reorder_index[-select_num:]` gather of model/quantize.py:237-241,262-267
+    for tag, (M, KQ, KE, dist, seed) in {"d": (16, 512, 64, "A", 21), "e": (8, 768, 128, "B", 22)}.items():
+        x, idx16 = make_acts(M, KQ, KE, seed=seed, dist=dist)
+        idx = idx16.long()
+        assert not torch.equal(idx, torch.arange(KQ))
+        qx, scale_x, scale = refq.fake_reorder_quantize_x(x.float(), idx, KE)
+        g = torch.Generator().manual_seed(seed + 1)
+        w = (torch.randn(32, KQ, generator=g) * 0.02).to(torch.bfloat16).float()
+        qw, scale_w, sw = refq.fake_reorder_quantize_w(w, idx, KE)
+        out[tag + "_x_bits"] = x.view(torch.int16).numpy().view(np.uint16)
+        out[tag + "_idx"] = idx.numpy().astype(np.int32)
+        out[tag + "_KE"] = np.int32(KE)
+        out[tag + "_qx"] = qx.numpy().astype(np.float32)
+        out[tag + "_scale"] = np.float32(float(scale))
+        out[tag + "_w"] = w.numpy()
+        out[tag + "_qw"] = qw.numpy().astype(np.float32)
+        out[tag + "_sw"] = np.float32(float(sw))
     np.savez_compressed(os.path.join(HERE, "fakequant_reference.npz"), **out)
 
 

@@ -61,15 +61,16 @@ def test_gemm_vs_dequant_matmul(M, N, KQ, KE):
     _run_case(M, N, KQ, KE, seed=M + N)
 
 
-@pytest.mark.parametrize("variant", ["pair", "bn128", "bn256", "cluster22"])
+VARIANTS = {"pair": {"gemm_pair": 1, "gemm_splitk": 0}, "bn128": {"gemm_pair": 0, "gemm_bn": 128, "gemm_splitk": 0},
+            "bn256": {"gemm_pair": 0, "gemm_bn": 256, "gemm_splitk": 0}}
+
+
+@pytest.mark.parametrize("variant", sorted(VARIANTS))
 @pytest.mark.parametrize("M,N,KQ,KE", [(256, 256, 256, 0), (300, 520, 1024, 64), (77, 1000, 2048, 128), (1024, 768, 4096, 256)])
-def test_gemm_kernel_variants(monkeypatch, variant, M, N, KQ, KE):
-    """Every kernel family (cta_group::2 pair, single-CTA 128/256-wide, multicast cluster) on ragged shapes."""
-    env = {"pair": {"ARCQ_GEMM_PAIR": "1"}, "bn128": {"ARCQ_GEMM_PAIR": "0", "ARCQ_GEMM_CLUSTER": "0", "ARCQ_GEMM_BN": "128"},
-           "bn256": {"ARCQ_GEMM_PAIR": "0", "ARCQ_GEMM_CLUSTER": "0", "ARCQ_GEMM_BN": "256"},
-           "cluster22": {"ARCQ_GEMM_PAIR": "0", "ARCQ_GEMM_CLUSTER": "22"}}[variant]
-    for k, v in env.items():
-        monkeypatch.setenv(k, v)
+def test_gemm_kernel_variants(arcq_option, variant, M, N, KQ, KE):
+    """Every kernel family (cta_group::2 pair, single-CTA 128/256-wide) on ragged shapes."""
+    for k, v in VARIANTS[variant].items():
+        arcq_option(k, v)
     _run_case(M, N, KQ, KE, seed=M + N + 1)
 
 

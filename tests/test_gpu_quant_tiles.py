@@ -3,7 +3,7 @@
 The shape-driven dispatch (quant_tma.cu: launch_quant_tma) picks the 1-row tile for the small M the other parity tests
 use, so the 4- and 2-row tiles that real prefill sizes run (ldmatrix/stmatrix transposition, owned gather offsets,
 packed two-row arithmetic, the 64-channel tail step) are forced here through the experiment knob
-ARCQ_QUANT_TMA="R,threads,S,RT,CTAs/SM", and the default dispatch is checked once at a size where it picks them itself.
+arcq_set_option("quant_tile", "R,threads,S,RT,CTAs/SM"), and the default dispatch is checked once at a size where it picks them itself.
 Bit-exact against oracle/ (reference kernels: kernels/src/reorder.cu, down.cu, rmsnorm.cu).
 """
 import numpy as np
@@ -47,12 +47,12 @@ TILE_CASES = [
 
 
 @pytest.mark.parametrize("knob,M,KQ,KE,flavour", TILE_CASES)
-def test_forced_tile_quantize_x(monkeypatch, knob, M, KQ, KE, flavour):
+def test_forced_tile_quantize_x(arcq_option, knob, M, KQ, KE, flavour):
     from arcquant_b200 import agemm
     O = oracle.lib()
     x, idx = make_acts(M, KQ, KE, seed=M + KQ, dist="A")
     q_ref, sf_ref = O.quantize_x(bits(x), idx.numpy(), KE, flavour)
-    monkeypatch.setenv("ARCQ_QUANT_TMA", knob)
+    arcq_option("quant_tile", knob)
     q, sf = agemm.reorder_quantize_x(x.cuda(), idx.cuda(), KE, -1 if flavour is None else flavour)
     torch.cuda.synchronize()
     _check(q, sf, q_ref, sf_ref, M, KQ + KE, "quantize_x %s M=%d KQ=%d KE=%d" % (knob, M, KQ, KE))
@@ -60,12 +60,12 @@ def test_forced_tile_quantize_x(monkeypatch, knob, M, KQ, KE, flavour):
 
 @pytest.mark.parametrize("knob,N,KQ,KE", [("4,256,2,4,2", 520, 4096, 256), ("8,512,1,4,1", 300, 4096, 256), ("2,512,2,2,1", 260, 14336, 512),
                                           ("4,512,2,4,1", 300, 8192, 512)])
-def test_forced_tile_quantize_w(monkeypatch, knob, N, KQ, KE):
+def test_forced_tile_quantize_w(arcq_option, knob, N, KQ, KE):
     from arcquant_b200 import agemm
     O = oracle.lib()
     w, idx = make_acts(N, KQ, KE, seed=N + 1, dist="B")
     q_ref, sf_ref = O.quantize_w(bits(w), idx.numpy(), KE, None)
-    monkeypatch.setenv("ARCQ_QUANT_TMA", knob)
+    arcq_option("quant_tile", knob)
     q, sf = agemm.reorder_quantize_w(w.cuda(), idx.cuda(), KE)
     torch.cuda.synchronize()
     _check(q, sf, q_ref, sf_ref, N, KQ + KE, "quantize_w %s N=%d KQ=%d KE=%d" % (knob, N, KQ, KE))
@@ -88,7 +88,7 @@ RMS_CASES = [("8,512,1,4,1", 1300, 4096, 256), ("8,512,1,4,1", 140, 3584, 256), 
 
 
 @pytest.mark.parametrize("knob,M,H,KE", RMS_CASES)
-def test_forced_tile_rmsnorm_matches_one_row_tiles(monkeypatch, knob, M, H, KE):
+def test_forced_tile_rmsnorm_matches_one_row_tiles(arcq_option, knob, M, H, KE):
     """The 1-row tile kernel is pinned to the oracle by test_gpu_quant.py (with its rsqrt-ulp allowance); every other
     tile height runs the same reduction tree, so it must reproduce the 1-row result bit for bit."""
     from arcquant_b200 import agemm
@@ -96,9 +96,9 @@ def test_forced_tile_rmsnorm_matches_one_row_tiles(monkeypatch, knob, M, H, KE):
     x = (torch.randn(M, H, generator=g) * 3).to(torch.bfloat16).cuda()
     w = (1.0 + 0.1 * torch.randn(H, generator=g)).to(torch.bfloat16).cuda()
     idx = torch.randperm(H, generator=g).to(torch.int16).cuda()
-    monkeypatch.setenv("ARCQ_QUANT_TMA", "1,512,1,1,1")
+    arcq_option("quant_tile", "1,512,1,1,1")
     q1, sf1 = agemm.rmsnorm_quantize_x(x, w, 1e-6, idx, KE)
-    monkeypatch.setenv("ARCQ_QUANT_TMA", knob)
+    arcq_option("quant_tile", knob)
     q2, sf2 = agemm.rmsnorm_quantize_x(x, w, 1e-6, idx, KE)
     torch.cuda.synchronize()
     off = oracle.lib().sf_valid_offsets(M, H + KE)
@@ -106,7 +106,7 @@ def test_forced_tile_rmsnorm_matches_one_row_tiles(monkeypatch, knob, M, H, KE):
     assert np.array_equal(sf1.cpu().numpy()[off], sf2.cpu().numpy()[off]), "%s: scales differ" % knob
 
 
-def test_default_rmsnorm_at_prefill_size_matches_one_row_tiles(monkeypatch):
+def test_default_rmsnorm_at_prefill_size_matches_one_row_tiles(arcq_option):
     from arcquant_b200 import agemm
     M, H, KE = 2500, 4096, 256
     g = torch.Generator().manual_seed(5)
@@ -114,7 +114,7 @@ def test_default_rmsnorm_at_prefill_size_matches_one_row_tiles(monkeypatch):
     w = (1.0 + 0.1 * torch.randn(H, generator=g)).to(torch.bfloat16).cuda()
     idx = torch.randperm(H, generator=g).to(torch.int16).cuda()
     q2, sf2 = agemm.rmsnorm_quantize_x(x, w, 1e-6, idx, KE)
-    monkeypatch.setenv("ARCQ_QUANT_TMA", "1,512,1,1,1")
+    arcq_option("quant_tile", "1,512,1,1,1")
     q1, sf1 = agemm.rmsnorm_quantize_x(x, w, 1e-6, idx, KE)
     torch.cuda.synchronize()
     off = oracle.lib().sf_valid_offsets(M, H + KE)

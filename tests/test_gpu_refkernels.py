@@ -46,7 +46,8 @@ def _ref_quant(R, fn, x, idx, KE):
     return q.cpu().numpy(), sf.cpu().numpy()
 
 
-X_CASES = [(128, 4096, 256, "A"), (300, 4096, 0, "A"), (77, 4096, 1024, "B"), (1, 4096, 64, "A"), (256, 2048, 128, "small"),
+X_CASES = [(2500, 4096, 256, "A"), (1290, 14336, 512, "A"), (1300, 3584, 256, "A"), (1400, 8192, 512, "B"),  # multi-row tiles
+           (128, 4096, 256, "A"), (300, 4096, 0, "A"), (77, 4096, 1024, "B"), (1, 4096, 64, "A"), (256, 2048, 128, "small"),
            (130, 14336, 512, "A"), (64, 3584, 256, "A"), (33, 18944, 512, "B"), (20, 28672, 1024, "A"), (40, 27648, 512, "A"),
            (129, 8192, 512, "A"), (50, 5120, 320, "A"), (16, 11008, 1024, "A"), (24, 13824, 512, "A"), (9, 3072, 192, "B")]
 
@@ -86,7 +87,10 @@ def test_w_ours_equals_reference_kernel_equals_oracle(R, N, KQ, KE):
     assert np.array_equal(q_o, q_ref) and np.array_equal(sf_valid(O, sf_o, N, K), sf_valid(O, sf_ref, N, K))
 
 
-@pytest.mark.parametrize("M,H,KE", [(128, 4096, 256), (37, 3584, 256), (200, 2048, 0), (64, 8192, 512), (9, 5120, 64)])
+@pytest.mark.parametrize("M,H,KE", [(128, 4096, 256), (37, 3584, 256), (200, 2048, 0), (64, 8192, 512), (9, 5120, 64),
+                                    # prefill sizes: the shape-driven dispatch picks the multi-row tiles here (M >= 1184)
+                                    (1300, 4096, 256), (2500, 3584, 256), (1290, 8192, 512), (1184, 2048, 128), (1500, 5120, 320),
+                                    (4096 + 77, 4096, 256)])
 def test_rmsnorm_ours_equals_reference_kernel(R, M, H, KE):
     """Same device, same rsqrtf, same reduction order -> the fused rmsnorm variant must match bit for bit."""
     from arcquant_b200 import agemm

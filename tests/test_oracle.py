@@ -104,12 +104,16 @@ def test_flavour_table(O):
 
 # ---- the fake-quant restatement against the real model/quantize.py -------------------------------------
 
-@pytest.mark.parametrize("tag", ["a", "b", "c"])
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d", "e"])
 def test_fakequant_restatement_matches_reference_module(tag):
+    """a-c: identity order (outliers last); d, e: a real permutation, so the reference's `reorder_index[-select_num:]`
+    gather (model/quantize.py:237-241,262-267) is pinned too."""
     d = np.load(os.path.join(GOLD, "fakequant_reference.npz"))
     x = torch.from_numpy(oracle.bf16_bits_to_f32(d[tag + "_x_bits"]))
     KE = int(d[tag + "_KE"])
-    idx = torch.arange(x.shape[1])
+    idx = torch.from_numpy(d[tag + "_idx"].astype(np.int64)) if tag + "_idx" in d else torch.arange(x.shape[1])
+    if tag in ("d", "e"):
+        assert not torch.equal(idx, torch.arange(x.shape[1]))
     qx, _, scale = fq.fake_reorder_quantize_x(x, idx, KE)
     assert np.float32(float(scale)) == d[tag + "_scale"]
     assert np.array_equal(qx.numpy().astype(np.float32), d[tag + "_qx"])
@@ -252,3 +256,25 @@ def test_div6_exact():
         rem = Fraction(float(rn32(a - 6 * q0)))
         q = rn32(q0 + rem * R)
         assert q.view(np.uint32) == rn32(a / 6).view(np.uint32), hex(h)
+
+
+# ---- the torch sampled-row GEMM oracle (oracle/torchref.py) against the C oracle --------------------------------
+
+def test_torchref_matches_c_oracle(O):
+    from oracle import torchref as T
+    rng = np.random.default_rng(5)
+    M, N, K = 200, 136, 320
+    qa = rng.integers(0, 256, (M, K // 2), dtype=np.uint8)
+    qb = rng.integers(0, 256, (N, K // 2), dtype=np.uint8)
+    sfa = rng.integers(0, 0x7f, O.sf_bytes(M, K), dtype=np.uint8)   # includes E4M3 subnormals (exponent field 0)
+    sfb = rng.integers(0x20, 0x50, O.sf_bytes(N, K), dtype=np.uint8)
+    rows = torch.tensor([0, 1, 31, 32, 127, 128, 129, 199])
+    da = T.dequant_rows(torch.from_numpy(qa), torch.from_numpy(sfa), rows, K).numpy()
+    assert np.array_equal(da, O.dequant(qa, sfa, K)[rows.numpy()].astype(np.float64))
+    ref, mag = T.gemm_rows(torch.from_numpy(qa), torch.from_numpy(sfa), torch.from_numpy(qb), torch.from_numpy(sfb), rows, 0.37)
+    full = O.gemm(qa, qb, sfa, sfb, 0.37)
+    assert np.allclose(ref.numpy(), full[rows.numpy()], rtol=1e-12, atol=0)
+    assert (mag.numpy() >= np.abs(ref.numpy()) - 1e-9).all()
+    assert np.array_equal(T.sf_offsets(torch.arange(M), K).numpy(), O.sf_valid_offsets(M, K))
+    r = T.sample_rows(1000)
+    assert r[0] == 0 and r[-1] == 999 and all(((r >= b * 128) & (r < b * 128 + 128)).sum() >= 1 for b in range(8))
