@@ -172,12 +172,11 @@ def _c_matmul(A, B, SFA, SFB, scale, col_scale=None, epilogue: int = 0, out=None
         raise RuntimeError("scale-factor buffers too small for M=%d N=%d K=%d" % (M, N, K))
     alpha_dev = 0
     alpha = 0.0
-    if isinstance(scale, torch.Tensor) and scale.is_cuda:
-        if scale.dtype != torch.float32 or scale.numel() != 1 or scale.device != A.device:
-            raise RuntimeError("a device `scale` must be one float32 on %s" % A.device)
-        alpha_dev = scale.data_ptr()
+    if (isinstance(scale, torch.Tensor) and scale.is_cuda and scale.dtype == torch.float32 and scale.numel() == 1
+            and scale.device == A.device):
+        alpha_dev = scale.data_ptr()  # read by the kernel: no host sync
     else:
-        alpha = float(scale)
+        alpha = float(scale)  # Python float, or any other tensor through .item() like the reference's `const float scale`
     cs = 0
     if col_scale is not None:
         _need(col_scale, "col_scale", torch.float32, 1)

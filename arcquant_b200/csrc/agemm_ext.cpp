@@ -131,12 +131,14 @@ torch::Tensor matmul(const torch::Tensor &A, const torch::Tensor &B, const torch
   float alpha = 0.0f;
   const float *alpha_dev = nullptr;
   torch::Tensor scale_t;
-  if (py::isinstance<torch::Tensor>(scale) && (scale_t = scale.cast<torch::Tensor>()).is_cuda()) {
-    TORCH_CHECK(scale_t.scalar_type() == torch::kFloat32 && scale_t.numel() == 1 && scale_t.device() == A.device(),
-                "a device `scale` must be one float32 on ", A.device());
-    alpha_dev = scale_t.data_ptr<float>();
+  if (py::isinstance<torch::Tensor>(scale) && (scale_t = scale.cast<torch::Tensor>()).is_cuda() &&
+      scale_t.scalar_type() == torch::kFloat32 && scale_t.numel() == 1 && scale_t.device() == A.device()) {
+    alpha_dev = scale_t.data_ptr<float>();  // read by the kernel: no host sync
+  } else if (py::isinstance<torch::Tensor>(scale)) {
+    TORCH_CHECK(scale_t.defined() ? scale_t.numel() == 1 : scale.cast<torch::Tensor>().numel() == 1, "`scale` must hold one value");
+    alpha = (scale_t.defined() ? scale_t : scale.cast<torch::Tensor>()).item<float>();  // any other tensor: .item(), a D2H sync like the reference's `const float scale` (:104)
   } else {
-    alpha = scale.cast<float>();  // Python float, or a CPU / 0-dim tensor through __float__ like the reference (:104)
+    alpha = scale.cast<float>();
   }
   const float *cs = nullptr;
   if (col_scale.has_value()) {

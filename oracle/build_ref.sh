@@ -3,7 +3,11 @@
 # probe of the reference's arithmetic library (CUTLASS converters + CuTe SF layout) and (b) the reference's own
 # quantise kernels, unchanged, for sm_100a, behind oracle/refkernels_shim.cu.  Outputs only into oracle/_ref/
 # (git-ignored; travels to the GPU box with the gpurun snapshot).  No reference source is copied.
-#   usage: oracle/build_ref.sh [probe|kernels|all]   (default: all; kernels take ~4 min of nvcc)
+# (c) "py": the reference's own PYTHON CALLERS of the extension (model/qLinearLayer.py + the model/quantize.py it imports,
+# kernels/main.py, benchmarks/modeling_arc.py) copied UNMODIFIED into the git-ignored oracle/_ref/py/ so that the -m gpu
+# test tests/test_gpu_ref_callers.py can run them on top of THIS repo's `agemm` on the GPU box, where /root/reference does
+# not exist.  They never enter the repository's history (oracle/_ref/ is in .gitignore).
+#   usage: oracle/build_ref.sh [probe|kernels|py|all]   (default: all; kernels take ~4 min of nvcc)
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF=/root/reference
@@ -18,6 +22,11 @@ if [ "$WHAT" = probe ] || [ "$WHAT" = all ]; then
     $NVCC -std=c++17 -O1 -w --expt-relaxed-constexpr -arch=sm_100a $INC "$HERE/ref_probe.cu" -o "$OUT/ref_probe"
   fi
   "$OUT/ref_probe" "$OUT/tables"
+fi
+if [ "$WHAT" = py ] || [ "$WHAT" = all ]; then
+  mkdir -p "$OUT/py"
+  cp "$REF/model/qLinearLayer.py" "$REF/model/quantize.py" "$REF/kernels/main.py" "$REF/benchmarks/modeling_arc.py" "$OUT/py/"
+  echo "build_ref: copied the reference callers into $OUT/py (git-ignored)"
 fi
 if [ "$WHAT" = kernels ] || [ "$WHAT" = all ]; then
   FLAGS="-std=c++17 -O2 -w --expt-relaxed-constexpr -Xcompiler -fPIC -Xcompiler -fpermissive -gencode arch=compute_100a,code=sm_100a $INC"

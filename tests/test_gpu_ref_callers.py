@@ -1,0 +1,105 @@
+"""The reference's OWN Python callers, unmodified, on top of this repo's `agemm` (QLinearLayer is
+"kept verbatim as the consumer in parity tests"; VERDICT r1 missing #7).
+
+oracle/build_ref.sh copies model/qLinearLayer.py (+ the model/quantize.py it star-imports), kernels/main.py and
+benchmarks/modeling_arc.py from /root/reference into the git-ignored oracle/_ref/py/ (they travel to the GPU box with the
+snapshot, never into the history).  Here they import `agemm` -- which resolves to THIS repo's module -- and run:
+
+* `QLinearLayer` (model/qLinearLayer.py:29-77) built from an nn.Linear, fed by the reference's own
+  `NVFP4_reorder_quantize_x` expression (model/qLlamaLayer.py:73-77), against the fp32 linear;
+* kernels/main.py:7-48, the reference's only end-to-end script: MSE of the quantised product falls as KE grows.
+"""
+import contextlib
+import importlib
+import io
+import os
+import re
+import sys
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PY = os.path.join(ROOT, "oracle", "_ref", "py")
+
+
+@pytest.fixture(scope="module")
+def refpy():
+    if not os.path.exists(os.path.join(PY, "qLinearLayer.py")):
+        pytest.skip("oracle/_ref/py not present (oracle/build_ref.sh py)")
+    import agemm  # noqa: F401  THIS repo's module under the reference's module name
+    assert os.path.dirname(os.path.abspath(agemm.__file__)).startswith(ROOT)
+    sys.path.insert(0, PY)
+    try:
+        yield importlib.import_module("qLinearLayer")
+    finally:
+        sys.path.remove(PY)
+
+
+def test_reference_qlinearlayer_runs_on_this_agemm(refpy):
+    import agemm
+    torch.manual_seed(0)
+    dev = "cuda"
+    in_f, out_f, M, KE = 4096, 1024, 256, 256
+    lin = torch.nn.Linear(in_f, out_f, bias=True, device=dev, dtype=torch.bfloat16)
+    x = torch.randn(2, M // 2, in_f, device=dev, dtype=torch.bfloat16)
+    x[..., :KE] *= 12
+    idx = torch.argsort(x.reshape(-1, in_f).float().abs().amax(0), stable=True)
+    layer = refpy.QLinearLayer(lin, KE, idx.clone())                      # the reference's class, unmodified
+    assert layer.W.dtype == torch.uint8 and tuple(layer.W.shape) == (out_f, (in_f + KE) // 2)
+    # the reference's NVFP4_reorder_quantize_x, verbatim (model/qLlamaLayer.py:73-77)
+    x2 = x.reshape(-1, in_f)
+    scale = torch.max(x2.abs()).float() / (448.0 * 6.0)
+    qx, scale_x = agemm.reorder_quantize_x(x2 / scale, idx.to(torch.int16), KE)
+    y = layer((qx, scale_x, scale, 2, M // 2))                             # -> agemm.matmul(..., scale * self.scale) + bias
+    ref = F.linear(x.float(), lin.weight.float(), lin.bias.float())
+    assert y.shape == ref.shape and y.dtype == torch.bfloat16
+    rel = float((y.float() - ref).norm() / ref.norm())
+    assert rel < 0.12, rel
+    # and the fused pre-scale is a drop-in for those three lines: same bytes, same scale
+    q2, s2, sc2 = agemm.reorder_quantize_x_scaled(x2, idx.to(torch.int16), KE, mode=agemm.PRESCALE_BF16_DIVISOR)
+    assert torch.equal(q2, qx) and float(sc2) == float(scale)
+    y2 = layer((q2, s2, sc2.reshape(()), 2, M // 2))
+    assert torch.equal(y2, y)
+
+
+def test_reference_main_py_mse_falls_with_ke(refpy, monkeypatch):
+    """kernels/main.py, executed as is (its time.sleep(1) per point patched out): 17 KE points 0..4096."""
+    import time
+    monkeypatch.setattr(time, "sleep", lambda s: None)
+    src = open(os.path.join(PY, "main.py")).read()
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        exec(compile(src, os.path.join(PY, "main.py"), "exec"), {"__name__": "__main__"})
+    mse = [float(m) for m in re.findall(r"MSE\(k=\s*\d+\s*\):\s*([0-9.eE+-]+)", buf.getvalue())]
+    assert len(mse) == 17, buf.getvalue()[-500:]
+    assert mse[-1] < 0.25 * mse[0], mse                    # residual channels buy accuracy
+    assert all(b <= a * 1.02 for a, b in zip(mse, mse[1:])), mse   # monotone (2 % slack for ties in the plateau)
+
+
+def test_reference_speed_model_pieces_run_on_this_agemm(refpy):
+    """benchmarks/modeling_arc.py: its QLinearLayer / LlamaRMSNorm / reorder_quantize_x (the speed path's callers) --
+    skipped when this image's transformers / flashinfer no longer export what the file imports."""
+    sys.path.insert(0, PY)
+    try:
+        m = importlib.import_module("modeling_arc")
+    except Exception as e:  # noqa: BLE001
+        pytest.skip("modeling_arc.py does not import against this image's transformers/flashinfer: %s" % str(e)[:120])
+    finally:
+        sys.path.remove(PY)
+    H, N, KE, bsz, q_len = 4096, 1024, 256, 2, 192
+    norm = m.LlamaRMSNorm(H, 1e-6, KE).cuda()
+    with torch.no_grad():
+        norm.weight.fill_(1.0)
+    lin = m.QLinearLayer(H, N, False, KE)                                  # synthetic B = 0, SFB = 127 (modeling_arc.py:44-45)
+    h = torch.randn(bsz, q_len, H, device="cuda", dtype=torch.bfloat16)
+    A, SFA, b_, q_ = norm(h)                                               # agemm.rmsnorm_quantize_x
+    assert (b_, q_) == (bsz, q_len) and tuple(A.shape) == (bsz * q_len, (H + KE) // 2)
+    y = lin((A, SFA, b_))                                                  # agemm.matmul with alpha = bsz (the benchmark's quirk)
+    assert tuple(y.shape) == (bsz * q_len, N) and bool((y == 0).all())     # zero weights -> exactly zero
+    qx, sx, sc = m.reorder_quantize_x(h.reshape(-1, H), lin.reorder_index, KE)
+    y2 = lin((qx, sx, sc))
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(y2).all())

@@ -1,0 +1,60 @@
+"""Host-side bookkeeping of the fused launches, on the CPU (no kernels): concatenating / interleaving already-quantised
+weights must move whole 128-row scale-factor blocks, so that dequantising the fused operand gives back the parts."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from arcquant_b200 import agemm
+from tests._util import bits, make_acts, make_weights
+
+
+def _quant_w(O, N, KQ, KE, idx, seed):
+    w, sw = make_weights(N, KQ, seed=seed)
+    q, sf = O.quantize_w(bits(w), idx.numpy(), KE)
+    return torch.from_numpy(q), torch.from_numpy(sf), sw
+
+
+def test_fuse_weights_moves_whole_scale_blocks():
+    O = oracle.lib()
+    KQ, KE = 512, 64
+    K = KQ + KE
+    _, idx = make_acts(8, KQ, KE, seed=1)
+    parts = [_quant_w(O, n, KQ, KE, idx, 10 + i) for i, n in enumerate((256, 128, 384))]
+    qw, sfw, cs = agemm.fuse_weights(parts)
+    assert qw.shape == (768, K // 2) and sfw.numel() == (768 // 128 + 1) * 128 * K // 16 and cs.shape == (768,)
+    deq = O.dequant(qw.numpy(), sfw.numpy(), K)
+    n0 = 0
+    for q, sf, sw in parts:
+        n = q.shape[0]
+        assert np.array_equal(deq[n0:n0 + n], O.dequant(q.numpy(), sf.numpy(), K))
+        assert torch.all(cs[n0:n0 + n] == torch.tensor(sw, dtype=torch.float32))
+        n0 += n
+    with pytest.raises(RuntimeError):
+        agemm.fuse_weights([_quant_w(O, 200, KQ, KE, idx, 3), parts[0]])   # 200 rows: not whole scale blocks
+
+
+def test_interleave_gate_up_layout():
+    O = oracle.lib()
+    KQ, KE, I = 256, 64, 384
+    K = KQ + KE
+    _, idx = make_acts(8, KQ, KE, seed=2)
+    gate, up = _quant_w(O, I, KQ, KE, idx, 20), _quant_w(O, I, KQ, KE, idx, 21)
+    qw, sfw, cs = agemm.interleave_gate_up(gate, up)
+    assert qw.shape == (2 * I, K // 2) and cs.shape == (2 * I,)
+    deq = O.dequant(qw.numpy(), sfw.numpy(), K)
+    dg, du = O.dequant(gate[0].numpy(), gate[1].numpy(), K), O.dequant(up[0].numpy(), up[1].numpy(), K)
+    for j in range(I // 128):   # rows [256 j, +128) = gate block j, rows [256 j + 128, +128) = up block j
+        assert np.array_equal(deq[256 * j:256 * j + 128], dg[128 * j:128 * j + 128])
+        assert np.array_equal(deq[256 * j + 128:256 * j + 256], du[128 * j:128 * j + 128])
+        assert torch.all(cs[256 * j:256 * j + 128] == torch.tensor(gate[2], dtype=torch.float32))
+        assert torch.all(cs[256 * j + 128:256 * j + 256] == torch.tensor(up[2], dtype=torch.float32))
+
+
+def test_bench_layer_items_and_sampling():
+    import bench
+    items = bench.layer_items("llama3-8b")
+    assert [(n, kq, ke) for n, kq, ke, _ in items] == [("qkv", 4096, 256), ("o", 4096, 256), ("gate_up", 4096, 256), ("down", 14336, 512)]
+    assert sum(2.0 * 8192 * n * (kq + ke) for _, kq, ke, ns in items for n in ns) == pytest.approx(3.771e12, rel=1e-3)
+    assert bench.quant_bytes(8192, 4096, 256) == 8192 * 10640 + 2 * 4096
+    assert bench.layer_items("llama3-70b")[3][1] == 28672
