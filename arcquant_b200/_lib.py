@@ -27,6 +27,10 @@ SIGNATURES = {
     "arcq_absmax": (_I32, [_VP, _I64, _VP, _VP]),
     "arcq_quantize_x_scaled": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _I32, _VP, _VP, _VP, _VP]),
     "arcq_set_option": (_I32, [ctypes.c_char_p, ctypes.c_char_p]),
+    "arcq_plan_entries": (_I64, [_I32]),
+    "arcq_plan_build": (_I32, [_VP, _I32, _VP]),
+    "arcq_plan_max_conflict": (_I32, [_VP, _I32, _I32, _VP]),
+    "arcq_quantize_x_ex": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _VP, _I32, _VP, _VP, _VP, _VP]),
     "arcq_launch_count": (_I64, []),
     "arcq_last_error": (ctypes.c_char_p, []),
     "arcq_version": (ctypes.c_char_p, []),

@@ -29,7 +29,7 @@ from . import _lib
 
 __all__ = [
     "matmul", "reorder_quantize_x", "reorder_quantize_w", "rmsnorm_quantize_x", "reorder_quantize_x_scaled", "absmax",
-    "sf_bytes", "flavour_for_kq", "launch_count", "set_option", "fuse_weights", "interleave_gate_up",
+    "sf_bytes", "flavour_for_kq", "launch_count", "set_option", "use_plans", "fuse_weights", "interleave_gate_up",
     "EPILOGUE_NONE", "EPILOGUE_SWIGLU", "PRESCALE_FP32", "PRESCALE_BF16_DIVISOR", "FLAVOUR_16", "FLAVOUR_32", "BACKEND",
 ]
 
@@ -225,6 +225,10 @@ if _ext is not None:
     flavour_for_kq = _ext.flavour_for_kq
     launch_count = _ext.launch_count
     set_option = _ext.set_option
+    use_plans = _ext.use_plans
+    plan_build = _ext.plan_build
+    plan_max_conflict = _ext.plan_max_conflict
+    reorder_quantize_x_planned = _ext.reorder_quantize_x_planned
     for _n in _KV:
         globals()[_n] = getattr(_ext, _n)
 else:
@@ -239,6 +243,10 @@ else:
     flavour_for_kq = _c_flavour_for_kq
     launch_count = _c_launch_count
     set_option = _c_set_option
+
+    def use_plans(on):  # the ctypes binding never builds placement plans
+        return None
+
     for _n in _KV:
         globals()[_n] = _not_on_this_path(_n)
 

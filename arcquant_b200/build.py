@@ -17,7 +17,12 @@ INCLUDE = os.path.join(_ROOT, "include")
 LIB = os.path.join(_HERE, "libarcq_b200.so")
 EXT = os.path.join(_HERE, "_agemm_ext.so")          # compiled pybind11/torch module over the C ABI (csrc/agemm_ext.cpp)
 EXT_NAME = "_agemm_ext"
-SOURCES = ["runtime.cu", "quant.cu", "quant_tma.cu", "gemm.cu", "gemm_pair.cu", "gemm_splitk.cu"]
+# (tile rows R, rows per item RT, threads, CTAs per SM) of the TMA-staged quantise kernel: one object file each
+QUANT_CFGS = [(4, 4, 256, 2), (4, 4, 512, 1), (2, 2, 256, 2), (2, 2, 512, 1), (1, 1, 512, 1), (8, 8, 512, 1), (8, 4, 512, 1)]
+# source file, or (source file, extra nvcc flags, object name)
+SOURCES = ["runtime.cu", "plan.cu", "quant.cu", "quant_tma.cu", "gemm.cu", "gemm_pair.cu", "gemm_splitk.cu"] + [
+    ("quant_tma_cfg.cu", ["-DARCQ_CFG_R=%d" % r, "-DARCQ_CFG_RT=%d" % rt, "-DARCQ_CFG_TH=%d" % th, "-DARCQ_CFG_MB=%d" % mb],
+     "quant_tma_cfg_%d_%d_%d_%d.o" % (r, rt, th, mb)) for r, rt, th, mb in QUANT_CFGS]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-I" + INCLUDE, "-I" + CSRC,
@@ -38,7 +43,7 @@ def _fingerprint() -> str:
             if name.endswith((".cu", ".cuh", ".h", ".cpp")):
                 with open(os.path.join(root, name), "rb") as f:
                     h.update(name.encode() + b"\0" + f.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(NVCC_FLAGS).encode() + repr(SOURCES).encode())
     return h.hexdigest()
 
 
@@ -99,12 +104,13 @@ def _build_locked(force: bool, verbose: bool) -> str:
     objdir = os.path.join(_HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     procs = []
-    for src in SOURCES:
+    for entry in SOURCES:
+        src, extra, oname = entry if isinstance(entry, tuple) else (entry, [], entry.replace(".cu", ".o"))
         path = os.path.join(CSRC, src)
         if not os.path.exists(path):
             raise FileNotFoundError(path)
-        obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
+        obj = os.path.join(objdir, oname)
+        cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", path, "-o", obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)
     for cmd, p in procs:

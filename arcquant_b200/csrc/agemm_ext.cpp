@@ -10,10 +10,14 @@
 //     absmax, set_option, sf_bytes, flavour_for_kq, launch_count.
 // This file is glue only: no arithmetic happens here, and there is no CPU path.
 #include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGraphsC10Utils.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <torch/extension.h>
 
+#include <mutex>
 #include <tuple>
+#include <unordered_map>
+#include <vector>
 
 #include "arcq.h"
 
@@ -36,6 +40,36 @@ int64_t sf_bytes(int64_t rows, int64_t K) { return arcq_sf_bytes(rows, K); }
 
 void *stream_of(const torch::Tensor &t) { return (void *)at::cuda::getCurrentCUDAStream(t.get_device()).stream(); }
 
+// ---- placement plans (include/arcq.h: arcq_plan_*): one per reorder_index, built on first use, kept on the device ----
+// Keyed by (device, data pointer, KQ).  A plan built for an index whose storage was later reused by another index of the
+// same length is still a valid placement (the kernel needs a bijection, nothing more), so a stale hit costs speed only.
+struct PlanKey {
+  const void *ptr; int64_t kq; int dev;
+  bool operator==(const PlanKey &o) const { return ptr == o.ptr && kq == o.kq && dev == o.dev; }
+};
+struct PlanKeyHash { size_t operator()(const PlanKey &k) const { return std::hash<const void *>()(k.ptr) ^ (size_t)(k.kq * 1315423911u) ^ (size_t)k.dev; } };
+std::mutex g_plan_mu;
+std::unordered_map<PlanKey, torch::Tensor, PlanKeyHash> g_plans;
+bool g_plans_enabled = true;
+
+const uint16_t *plan_for(const torch::Tensor &idx, int64_t KQ) {
+  if (!g_plans_enabled || KQ % 128 || KQ > 32768) return nullptr;   // no tile height has a usable section
+  const PlanKey key{idx.data_ptr(), KQ, (int)idx.get_device()};
+  std::lock_guard<std::mutex> lock(g_plan_mu);
+  auto it = g_plans.find(key);
+  if (it != g_plans.end()) return it->second.defined() ? reinterpret_cast<const uint16_t *>(it->second.data_ptr<int16_t>()) : nullptr;
+  if (c10::cuda::currentStreamCaptureStatusMayInitCtx() != c10::cuda::CaptureStatus::None) return nullptr;  // building needs a D2H copy
+  torch::Tensor host = idx.to(torch::kCPU).contiguous();
+  std::vector<uint16_t> plan((size_t)arcq_plan_entries((int)KQ));
+  torch::Tensor dev_plan;   // stays undefined if the index is not a permutation: remembered, never retried
+  if (arcq_plan_build(host.data_ptr<int16_t>(), (int)KQ, plan.data()) == ARCQ_OK) {
+    dev_plan = torch::from_blob(plan.data(), {(int64_t)plan.size()}, torch::kInt16).clone().to(idx.device());
+  }
+  if (g_plans.size() > 4096) g_plans.clear();
+  g_plans.emplace(key, dev_plan);
+  return dev_plan.defined() ? reinterpret_cast<const uint16_t *>(dev_plan.data_ptr<int16_t>()) : nullptr;
+}
+
 enum QuantKind { KIND_X, KIND_W };
 
 std::tuple<torch::Tensor, torch::Tensor> quant(QuantKind kind, const torch::Tensor &X, const torch::Tensor &reorder_index, int KE,
@@ -51,7 +85,8 @@ std::tuple<torch::Tensor, torch::Tensor> quant(QuantKind kind, const torch::Tens
   auto SF = torch::empty({sf_bytes(M, K)}, opt);
   const int rc = kind == KIND_W
                      ? arcq_quantize_w(X.data_ptr(), M, (int)KQ, reorder_index.data_ptr<int16_t>(), KE, flavour, Q.data_ptr(), SF.data_ptr(), stream_of(X))
-                     : arcq_quantize_x(X.data_ptr(), M, (int)KQ, reorder_index.data_ptr<int16_t>(), KE, flavour, Q.data_ptr(), SF.data_ptr(), stream_of(X));
+                     : arcq_quantize_x_ex(X.data_ptr(), M, (int)KQ, reorder_index.data_ptr<int16_t>(), KE, flavour, plan_for(reorder_index, KQ), nullptr, 0,
+                                          Q.data_ptr(), SF.data_ptr(), nullptr, stream_of(X));
   fail(rc, kind == KIND_W ? "arcq_quantize_w" : "arcq_quantize_x");
   return std::make_tuple(Q, SF);
 }
@@ -111,8 +146,8 @@ std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> reorder_quantize_x_scale
   auto Q = torch::empty({M, K / 2}, opt);
   auto SF = torch::empty({sf_bytes(M, K)}, opt);
   auto scale = torch::empty({1}, torch::dtype(torch::kFloat32).device(X.device()));
-  fail(arcq_quantize_x_scaled(X.data_ptr(), M, (int)KQ, reorder_index.data_ptr<int16_t>(), KE, flavour, am.data_ptr<float>(), mode, Q.data_ptr(),
-                              SF.data_ptr(), scale.data_ptr<float>(), stream_of(X)),
+  fail(arcq_quantize_x_ex(X.data_ptr(), M, (int)KQ, reorder_index.data_ptr<int16_t>(), KE, flavour, plan_for(reorder_index, KQ), am.data_ptr<float>(),
+                          mode, Q.data_ptr(), SF.data_ptr(), scale.data_ptr<float>(), stream_of(X)),
        "arcq_quantize_x_scaled");
   return std::make_tuple(Q, SF, scale);
 }
@@ -193,6 +228,37 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("flavour_for_kq", [](int KQ) { return arcq_flavour_for_kq(KQ); }, py::arg("KQ"));
   m.def("launch_count", []() { return arcq_launch_count(); });
   m.def("set_option", &set_option, py::arg("name"), py::arg("value") = "");
+  m.def("use_plans", [](bool on) { std::lock_guard<std::mutex> lock(g_plan_mu); g_plans_enabled = on; },
+        "enable / disable the conflict-free placement plans of reorder_quantize_x (A/B; same bytes either way)", py::arg("on"));
+  m.def("plan_build", [](const torch::Tensor &idx) {
+          TORCH_CHECK(idx.scalar_type() == torch::kInt16 && idx.dim() == 1, "reorder_index must be a 1-D int16 tensor");
+          torch::Tensor host = idx.to(torch::kCPU).contiguous();
+          const int KQ = (int)host.numel();
+          torch::Tensor plan = torch::empty({arcq_plan_entries(KQ)}, torch::kInt16);
+          fail(arcq_plan_build(host.data_ptr<int16_t>(), KQ, reinterpret_cast<uint16_t *>(plan.data_ptr<int16_t>())), "arcq_plan_build");
+          return plan;
+        }, "host plan (int16 CPU tensor, 3 * KQ entries) of a reorder_index", py::arg("reorder_index"));
+  m.def("plan_max_conflict", [](const torch::Tensor &idx, int R, const torch::Tensor &plan) {
+          torch::Tensor host = idx.to(torch::kCPU).contiguous(), hp = plan.to(torch::kCPU).contiguous();
+          return arcq_plan_max_conflict(host.data_ptr<int16_t>(), (int)host.numel(), R, reinterpret_cast<const uint16_t *>(hp.data_ptr<int16_t>()));
+        }, py::arg("reorder_index"), py::arg("R"), py::arg("plan"));
+  m.def("reorder_quantize_x_planned", [](const torch::Tensor &X, const torch::Tensor &reorder_index, int KE, const torch::Tensor &plan, int flavour) {
+          need(X, "X", torch::kBFloat16, 2);
+          need(reorder_index, "reorder_index", torch::kInt16, 1);
+          need(plan, "plan", torch::kInt16, 1);
+          const int64_t M = X.size(0), KQ = X.size(1), K = KQ + KE;
+          TORCH_CHECK(reorder_index.numel() == KQ && plan.numel() == 3 * KQ && plan.device() == X.device() && reorder_index.device() == X.device(),
+                      "reorder_index / plan do not match X");
+          const c10::cuda::CUDAGuard guard(X.device());
+          auto opt = torch::dtype(torch::kUInt8).device(X.device());
+          auto Q = torch::empty({M, K / 2}, opt);
+          auto SF = torch::empty({sf_bytes(M, K)}, opt);
+          fail(arcq_quantize_x_ex(X.data_ptr(), M, (int)KQ, reorder_index.data_ptr<int16_t>(), KE, flavour,
+                                  reinterpret_cast<const uint16_t *>(plan.data_ptr<int16_t>()), nullptr, 0, Q.data_ptr(), SF.data_ptr(), nullptr, stream_of(X)),
+               "arcq_quantize_x_ex");
+          return std::make_tuple(Q, SF);
+        }, "reorder_quantize_x with an explicit device plan (tests: any bijection gives the same bytes)", py::arg("X"), py::arg("reorder_index"),
+        py::arg("KE"), py::arg("plan"), py::arg("flavour") = -1);
   m.def("version", []() { return std::string(arcq_version()); });
   for (const char *n : {"batch_decode_i4", "init_kv_i4", "append_kv_i4", "batch_decode_f16", "init_kv_f16", "append_kv_f16"})
     m.def(n, [n](const py::args &, const py::kwargs &) { not_on_this_path(n); });

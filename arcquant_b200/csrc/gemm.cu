@@ -198,6 +198,14 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       const int mt = tile % p.tiles_m, nt = tile / p.tiles_m;
       const int acc = tile_it % Cfg::ACC_STAGES;
       const uint32_t acc_ph = (tile_it / Cfg::ACC_STAGES) & 1;
+      // per-column scales of this warp's HC columns: lane l keeps columns l, l + 32, ... (already times alpha), loaded
+      // before the accumulator wait; a shuffle fetches the one a store needs
+      float sreg[HC / 32];
+#pragma unroll
+      for (int r = 0; r < HC / 32; ++r) {
+        const int c = nt * BN + half * HC + r * 32 + lane;
+        sreg[r] = (cs && c < p.N) ? __fmul_rn(alpha, __ldg(cs + c)) : alpha;
+      }
       ptx::mbar_wait(&tfull[acc], acc_ph);
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + half * HC;
@@ -219,9 +227,8 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int col = pass * PC + j * 8 + 2 * e;
             float s0 = alpha, s1 = alpha;
             if (cs) {
-              const int gc = nt * BN + half * HC + col;
-              if (gc < p.N) s0 = __fmul_rn(alpha, __ldg(cs + gc));
-              if (gc + 1 < p.N) s1 = __fmul_rn(alpha, __ldg(cs + gc + 1));
+              s0 = __shfl_sync(0xffffffffu, sreg[col >> 5], col & 31);
+              s1 = __shfl_sync(0xffffffffu, sreg[col >> 5], (col & 31) + 1);
             }
             __nv_bfloat162 h2 = __floats2bfloat162_rn(s0 * __uint_as_float(r[col >> 5][col & 31]),
                                                       s1 * __uint_as_float(r[col >> 5][(col & 31) + 1]));

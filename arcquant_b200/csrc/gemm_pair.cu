@@ -64,11 +64,29 @@ struct PParams {
 };
 
 // bf16(silu(g)) * u exactly as torch computes `F.silu(g) * u` on bf16 tensors: silu in fp32 (x / (1 + exp(-x)), IEEE
-// division, libdevice expf), rounded to bf16, then an fp32 multiply rounded to bf16
+// division, libdevice expf), rounded to bf16, then an fp32 multiply rounded to bf16.  For x < -89 expf(-x) is +inf and the
+// quotient is exactly -0; that case (and only the narrow band [-89, -80] next to it, where the quotient approaches the
+// denormal range) is kept away from the common path so that the IEEE division never takes its out-of-range subroutine:
+// saturated activations must not make the epilogue 10x slower.
 __device__ __forceinline__ float swiglu_bf16(float g, float u) {
   const float gb = __bfloat162float(__float2bfloat16_rn(g)), ub = __bfloat162float(__float2bfloat16_rn(u));
-  const float s = __bfloat162float(__float2bfloat16_rn(__fdiv_rn(gb, 1.0f + expf(-gb))));
+  const bool far = gb < -80.0f;
+  const float den = 1.0f + expf(far ? 0.0f : -gb);
+  float q = __fdiv_rn(gb, den);
+  if (far) q = gb < -89.0f ? -0.0f : __fdiv_rn(gb, 1.0f + expf(-gb));   // rare lanes only
+  const float s = __bfloat162float(__float2bfloat16_rn(q));
   return __fmul_rn(s, ub);
+}
+
+// scale of tile column c (0..HC-1 of this warp's block): lane l keeps columns l, l + 32, ... in registers (loaded once per
+// tile BEFORE the accumulator wait, already multiplied by alpha); a shuffle fetches the one a store needs
+template <int NREG>
+__device__ __forceinline__ void load_col_scales(float (&sreg)[NREG], const float *cs, float alpha, int col0, int N, int lane) {
+#pragma unroll
+  for (int r = 0; r < NREG; ++r) {
+    const int c = col0 + r * 32 + lane;
+    sreg[r] = (cs && c < N) ? __fmul_rn(alpha, __ldg(cs + c)) : alpha;
+  }
 }
 
 // SWIGLU: the 256 columns of a pair tile are 128 "gate" columns followed by the 128 "up" columns of the SAME 128
@@ -221,6 +239,19 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     PROF(long long ew = 0, eld = 0, et0 = clock64();)
     for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
       const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
+      // first tile column of this warp's register block (input columns of the GEMM, for the per-column scales)
+      const int in_col0 = pn * kBN + (SWIGLU ? half * (HC / 2) : half * HC);
+      const int out_col0 = SWIGLU ? pn * (kBN / 2) + half * (HC / 2) : in_col0;
+      float sreg[HC / 32];   // plain: columns [0, 128) of the block; SWIGLU: [0, 64) gate then [0, 64) up
+      if constexpr (SWIGLU) {
+        float sg[HC / 64], su[HC / 64];
+        load_col_scales(sg, cs, alpha, in_col0, p.N, lane);
+        load_col_scales(su, cs, alpha, in_col0 + HC, p.N, lane);
+#pragma unroll
+        for (int r = 0; r < HC / 64; ++r) { sreg[r] = sg[r]; sreg[HC / 64 + r] = su[r]; }
+      } else {
+        load_col_scales(sreg, cs, alpha, in_col0, p.N, lane);
+      }
       PROF(long long e0 = clock64();)
       ptx::mbar_wait(tfull, tile_it & 1);
       PROF(long long e1 = clock64(); ew += e1 - e0;)
@@ -238,9 +269,6 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader);
       PROF(eld += clock64() - e1;)
       const int row_base = (pm * 2 + (int)rank) * kRows + q * 32;
-      // first tile column of this warp's register block cb (input columns of the GEMM, for the per-column scales)
-      const int in_col0 = pn * kBN + (SWIGLU ? half * (HC / 2) : half * HC);
-      const int out_col0 = SWIGLU ? pn * (kBN / 2) + half * (HC / 2) : in_col0;
 #pragma unroll
       for (int pass = 0; pass < OUTC / kPC; ++pass) {
 #pragma unroll
@@ -253,18 +281,18 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
             if constexpr (SWIGLU) {
               float sg0 = alpha, sg1 = alpha, su0 = alpha, su1 = alpha;
               if (cs) {
-                const int gc = in_col0 + col;
-                if (gc + 1 < p.N) { sg0 = __fmul_rn(alpha, __ldg(cs + gc)); sg1 = __fmul_rn(alpha, __ldg(cs + gc + 1)); }
-                if (gc + HC + 1 < p.N) { su0 = __fmul_rn(alpha, __ldg(cs + gc + HC)); su1 = __fmul_rn(alpha, __ldg(cs + gc + HC + 1)); }
+                sg0 = __shfl_sync(0xffffffffu, sreg[col >> 5], col & 31);
+                sg1 = __shfl_sync(0xffffffffu, sreg[col >> 5], (col & 31) + 1);
+                su0 = __shfl_sync(0xffffffffu, sreg[HC / 64 + (col >> 5)], col & 31);
+                su1 = __shfl_sync(0xffffffffu, sreg[HC / 64 + (col >> 5)], (col & 31) + 1);
               }
               v0 = swiglu_bf16(sg0 * __uint_as_float(r[col >> 5][col & 31]), su0 * __uint_as_float(r[2 + (col >> 5)][col & 31]));
               v1 = swiglu_bf16(sg1 * __uint_as_float(r[col >> 5][(col & 31) + 1]), su1 * __uint_as_float(r[2 + (col >> 5)][(col & 31) + 1]));
             } else {
               float s0 = alpha, s1 = alpha;
               if (cs) {
-                const int gc = in_col0 + col;
-                if (gc < p.N) s0 = __fmul_rn(alpha, __ldg(cs + gc));
-                if (gc + 1 < p.N) s1 = __fmul_rn(alpha, __ldg(cs + gc + 1));
+                s0 = __shfl_sync(0xffffffffu, sreg[col >> 5], col & 31);
+                s1 = __shfl_sync(0xffffffffu, sreg[col >> 5], (col & 31) + 1);
               }
               v0 = s0 * __uint_as_float(r[col >> 5][col & 31]);
               v1 = s1 * __uint_as_float(r[col >> 5][(col & 31) + 1]);

@@ -335,7 +335,7 @@ extern "C" int arcq_quantize_x(const void *x, int64_t M, int KQ, const int16_t *
   flavour = resolve_flavour(flavour, KQ);
   if (int rc = check_common(x, M, KQ, idx, KE, flavour, qx, sfx)) return rc;
   if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, 0, 0.0f, (int)M, KQ, KE, 0, 0};
+  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, nullptr, 0, 0.0f, (int)M, KQ, KE, 0, 0};
   return dispatch_quant<false>(p, flavour, (cudaStream_t)stream);
 }
 
@@ -346,12 +346,18 @@ namespace arcq {
 __global__ void __launch_bounds__(256) absmax_kernel(const uint4 *__restrict__ x, int64_t n8, const uint16_t *tail, int ntail,
                                                       unsigned int *out_bits) {
   uint32_t m = 0;  // per-halfword running maximum of |bits|
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < n8; i += 4 * stride) {  // four independent 16-byte loads in flight per thread
+    const uint4 a = __ldcs(x + i), b = __ldcs(x + i + stride), c = __ldcs(x + i + 2 * stride), d = __ldcs(x + i + 3 * stride);
+    m = __vmaxu2(m, __vmaxu2(__vmaxu2(a.x & 0x7fff7fffu, a.y & 0x7fff7fffu), __vmaxu2(a.z & 0x7fff7fffu, a.w & 0x7fff7fffu)));
+    m = __vmaxu2(m, __vmaxu2(__vmaxu2(b.x & 0x7fff7fffu, b.y & 0x7fff7fffu), __vmaxu2(b.z & 0x7fff7fffu, b.w & 0x7fff7fffu)));
+    m = __vmaxu2(m, __vmaxu2(__vmaxu2(c.x & 0x7fff7fffu, c.y & 0x7fff7fffu), __vmaxu2(c.z & 0x7fff7fffu, c.w & 0x7fff7fffu)));
+    m = __vmaxu2(m, __vmaxu2(__vmaxu2(d.x & 0x7fff7fffu, d.y & 0x7fff7fffu), __vmaxu2(d.z & 0x7fff7fffu, d.w & 0x7fff7fffu)));
+  }
+  for (; i < n8; i += stride) {
     const uint4 v = __ldg(x + i);
-    m = __vmaxu2(m, v.x & 0x7fff7fffu);
-    m = __vmaxu2(m, v.y & 0x7fff7fffu);
-    m = __vmaxu2(m, v.z & 0x7fff7fffu);
-    m = __vmaxu2(m, v.w & 0x7fff7fffu);
+    m = __vmaxu2(m, __vmaxu2(__vmaxu2(v.x & 0x7fff7fffu, v.y & 0x7fff7fffu), __vmaxu2(v.z & 0x7fff7fffu, v.w & 0x7fff7fffu)));
   }
   if (blockIdx.x == 0 && threadIdx.x < ntail) m = __vmaxu2(m, (uint32_t)(tail[threadIdx.x] & 0x7fffu));
   uint32_t h = max(m & 0xffffu, m >> 16);
@@ -375,7 +381,7 @@ extern "C" int arcq_absmax(const void *x, int64_t n, float *amax_out, void *stre
   const int sms = sm_count();
   if (sms <= 0) return ARCQ_ECUDA;
   const int64_t n8 = n / 8;
-  int64_t blocks = (n8 + 255) / 256;
+  int64_t blocks = (n8 + 1023) / 1024;  // four loads per thread per round
   if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
   if (blocks < 1) blocks = 1;
   absmax_kernel<<<(int)blocks, 256, 0, st>>>((const uint4 *)x, n8, (const uint16_t *)x + n8 * 8, (int)(n - n8 * 8),
@@ -385,18 +391,31 @@ extern "C" int arcq_absmax(const void *x, int64_t n, float *amax_out, void *stre
   return ARCQ_OK;
 }
 
+// reorder_quantize_x with the optional extras: a placement plan (plan.cu) and / or the fused per-tensor pre-scale
+extern "C" int arcq_quantize_x_ex(const void *x, int64_t M, int KQ, const int16_t *idx, int KE, int flavour,
+                                  const uint16_t *plan_dev, const float *amax_dev, int prescale_mode, void *qx, void *sfx,
+                                  float *scale_out, void *stream) {
+  flavour = resolve_flavour(flavour, KQ);
+  if (int rc = check_common(x, M, KQ, idx, KE, flavour, qx, sfx)) return rc;
+  if (amax_dev && prescale_mode != ARCQ_PRESCALE_FP32 && prescale_mode != ARCQ_PRESCALE_BF16_DIVISOR) {
+    set_error("arcq_quantize_x_ex: unknown prescale_mode %d", prescale_mode);
+    return ARCQ_EINVAL;
+  }
+  if (plan_dev && ((uintptr_t)plan_dev & 1)) { set_error("arcq_quantize_x_ex: misaligned plan"); return ARCQ_EINVAL; }
+  if (M == 0) return ARCQ_OK;
+  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, plan_dev, amax_dev, scale_out, prescale_mode, 0.0f,
+                (int)M, KQ, KE, 0, 0};
+  if (!amax_dev) return dispatch_quant<false>(p, flavour, (cudaStream_t)stream);   // a plan is an optimisation: fallbacks ignore it
+  const int rc = launch_quant_tma(p, flavour, false, false, (cudaStream_t)stream);
+  if (rc == ARCQ_ENOSUP) set_error("arcq_quantize_x_ex: KQ=%d KE=%d is outside the TMA-staged kernel's shapes; pre-scale separately", KQ, KE);
+  return rc;
+}
+
 extern "C" int arcq_quantize_x_scaled(const void *x, int64_t M, int KQ, const int16_t *idx, int KE, int flavour,
                                       const float *amax_dev, int prescale_mode, void *qx, void *sfx, float *scale_out,
                                       void *stream) {
-  flavour = resolve_flavour(flavour, KQ);
-  if (int rc = check_common(x, M, KQ, idx, KE, flavour, qx, sfx)) return rc;
   if (!amax_dev) { set_error("arcq_quantize_x_scaled: amax_dev is null"); return ARCQ_EINVAL; }
-  if (prescale_mode != ARCQ_PRESCALE_FP32 && prescale_mode != ARCQ_PRESCALE_BF16_DIVISOR) { set_error("arcq_quantize_x_scaled: unknown prescale_mode %d", prescale_mode); return ARCQ_EINVAL; }
-  if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, amax_dev, scale_out, prescale_mode, 0.0f, (int)M, KQ, KE, 0, 0};
-  const int rc = launch_quant_tma(p, flavour, false, false, (cudaStream_t)stream);
-  if (rc == ARCQ_ENOSUP) set_error("arcq_quantize_x_scaled: KQ=%d KE=%d is outside the TMA-staged kernel's shapes; pre-scale separately", KQ, KE);
-  return rc;
+  return arcq_quantize_x_ex(x, M, KQ, idx, KE, flavour, nullptr, amax_dev, prescale_mode, qx, sfx, scale_out, stream);
 }
 
 extern "C" int arcq_quantize_w(const void *w, int64_t N, int KQ, const int16_t *idx, int KE, int flavour, void *qw,
@@ -404,7 +423,7 @@ extern "C" int arcq_quantize_w(const void *w, int64_t N, int KQ, const int16_t *
   flavour = resolve_flavour(flavour, KQ);
   if (int rc = check_common(w, N, KQ, idx, KE, flavour, qw, sfw)) return rc;
   if (N == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)w, idx, nullptr, (uint8_t *)qw, (uint8_t *)sfw, nullptr, nullptr, 0, 0.0f, (int)N, KQ, KE, 0, 0};
+  QuantParams p{(const uint16_t *)w, idx, nullptr, (uint8_t *)qw, (uint8_t *)sfw, nullptr, nullptr, nullptr, 0, 0.0f, (int)N, KQ, KE, 0, 0};
   return dispatch_quant<true>(p, flavour, (cudaStream_t)stream);
 }
 
@@ -417,7 +436,7 @@ extern "C" int arcq_rmsnorm_quantize_x(const void *x, const void *w, float eps, 
     return ARCQ_ENOSUP;
   }
   if (M == 0) return ARCQ_OK;
-  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, 0, eps, (int)M, H, KE, 0, 0};
+  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, nullptr, 0, eps, (int)M, H, KE, 0, 0};
   cudaStream_t st = (cudaStream_t)stream;
   if (use_tma()) {
     const int rc = launch_quant_tma(p, ARCQ_FLAVOUR_16, false, true, st);

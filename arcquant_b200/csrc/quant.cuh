@@ -10,6 +10,7 @@ struct QuantParams {
   const uint16_t *w;     // rmsnorm weight bf16 [KQ] (RMS only)
   uint8_t *q;            // [M, K/2]
   uint8_t *sf;           // swizzled scale bytes
+  const uint16_t *plan;  // nullable: conflict-free chunk positions (plan.cu); the launcher narrows it to one tile height's section
   const float *amax;     // PRESCALE only: device fp32 max|x| of the whole tensor (arcq_absmax)
   float *scale_out;      // PRESCALE only (nullable): receives amax / 2688, the per-tensor scale the GEMM alpha needs
   int prescale_mode;     // PRESCALE only: ARCQ_PRESCALE_FP32 / ARCQ_PRESCALE_BF16_DIVISOR
@@ -60,6 +61,10 @@ template <int R> __device__ __forceinline__ int chan_pos_m(int c) {
 }
 // bytes added to every staged row so that the 8 row addresses of one ldmatrix fall into 8 different 16-byte bank groups
 __host__ __device__ constexpr int stage_pad(int R) { return R == 8 ? 16 : R == 4 ? 32 : R == 2 ? 64 : 0; }
+
+// placement plans (plan.cu)
+bool plan_usable(int R, int KQ);
+int plan_section(int R);
 
 // TMA-staged kernel family (quant_tma.cu); returns ARCQ_ENOSUP for shapes it does not take
 int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream);

@@ -97,7 +97,9 @@ struct PrescaleCtx { float scale, rcp; bool slow; };
 // the fp32 value.  The caller says which expression it replaces (ARCQ_PRESCALE_* in include/arcq.h).
 static __device__ __forceinline__ PrescaleCtx make_prescale(float amax, bool bf16_divisor, float &scale_fp32) {
   PrescaleCtx c;
-  scale_fp32 = __fdiv_rn(amax, 2688.0f);  // torch.max(x.abs()).float() / (448.0 * 6.0)
+  // torch.max(x.abs()).float() / (448.0 * 6.0): dividing a CUDA tensor by a Python scalar is computed as a * (1 / b)
+  // (BinaryDivTrueKernel.cu, "if the second operand is a CPU scalar, compute a * reciprocal(b)"), both in fp32
+  scale_fp32 = __fmul_rn(amax, 1.0f / 2688.0f);
   c.scale = bf16_divisor ? __bfloat162float(__float2bfloat16_rn(scale_fp32)) : scale_fp32;
   c.rcp = __frcp_rn(c.scale);
   c.slow = !(amax >= 9.094947017729282e-13f && amax <= 1.152921504606847e18f) || (__float_as_uint(c.scale) & 0x7fffffu) == 0x7fffffu;

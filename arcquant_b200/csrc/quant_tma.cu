@@ -1,602 +1,19 @@
-// quant_tma.cu -- TMA-staged reorder + NVFP4 + ARC quantise kernel (sm_100a).
-//
-// Same arithmetic contract and output layout as quant.cu (reference
-// kernels/src/{reorder,down,rmsnorm}.cu).  Organisation:
-//
-//  * persistent CTAs (two per SM when the tile is small enough); a work item is R rows of one 128-row scale block;
-//  * ONE thread streams whole bf16 rows into a ring of row-major staging slots with cp.async.bulk (TMA, mbarrier
-//    complete_tx): the next tile(s) are in flight while the current one is quantised, with no registers tied up;
-//  * all threads transpose a landed slot (LDS.128 -> PRMT -> swizzled STS) into the channel-major tile
-//    ("[channel][R rows]") so the permuted gather is one 2R-byte shared load per channel for all R rows;
-//  * gather offsets come from a once-per-CTA table built from reorder_index; when a thread owns the same 16-group
-//    in every tile (KQ/16 <= threads) its 16 offsets live in registers for the whole kernel;
-//  * phase A = primary quantisation (one group x R rows per thread), phase B = ARC residuals spread over all
-//    threads as (group,row) items; amax/6 by exact FMA division, RN(1/sf) and sf from a 127-entry LUT;
-//  * scale bytes are assembled per tile in shared memory and leave as whole 4R-byte runs of the 128x4 layout.
-#include "quant.cuh"
-#include "quant_math.cuh"
-#include "ptx.cuh"
-
-// Work-skipping experiment bits exist only in -DARCQ_EXPERIMENT builds (scripts/build_variant.py); the product library
-// compiles them out, so it cannot be made to skip its work.
-#ifdef ARCQ_EXPERIMENT
-#include <stdlib.h>
-#define ARCQ_DBG(p, bit) (((p).debug & (bit)) != 0)
-#else
-#define ARCQ_DBG(p, bit) false
-#endif
+// quant_tma.cu -- shape-driven choice of the tile organisation of the TMA-staged quantise kernel (quant_tma.cuh).
+#include "quant_tma.cuh"
 
 namespace arcq {
 namespace {
 
-struct CarveT {  // shared-memory layout (bytes), computed identically on host and device
-  int lut, sfs, arc, tab, wtab, part, rstd, tile, stage, total;
-};
-__host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool tab32, int S) {
-  CarveT c;
-  int o = 128;                  // mbarriers full[S] (S <= 4)
-  c.lut = o; o += 2 * 128 * 4;  // rcp + sf LUTs
-  c.sfs = o; o += 2 * ((KQ + KE) / 64) * 4 * R;  // two scale staging buffers [chunk][lr][slot%4]
-  o = (o + 15) & ~15;
-  c.arc = o; o += (KE / 16) * R * 48;            // per ARC (group,row): 16 bf16 x, 2 code words, subtrahend scale
-#ifdef ARCQ_STASH_LRMAJOR
-  o += R * 16;  // experiment: [row][group] stash, rows padded by 16 bytes (conflict-free STS.128 and LDS.128)
-#endif
-  c.tab = o; o += KQ * (tab32 ? 4 : 2);
-  o = (o + 15) & ~15;
-  c.wtab = o; if (rms) o += KQ * 2;
-  o = (o + 15) & ~15;
-  c.part = o; if (rms) o += R * 512 * 4;
-  c.rstd = o; if (rms) o += 64;
-  o = (o + 127) & ~127;
-  c.tile = o; o += KQ * 2 * R;
-  c.stage = o; o += S * (KQ * 2 + stage_pad(R)) * R;
-  c.total = o;
-  return c;
-}
-
-// PS: fused per-tensor pre-scale (activations only): every gathered element becomes bf16(x / (amax / 2688)) first
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS>
-__global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantParams p, const int S) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  constexpr int CB = 2 * R;        // bytes of one channel chunk
-  constexpr int RP = (R + 1) / 2;  // 32-bit words per chunk
-  constexpr int TPB = 128 / R;     // tiles per 128-row block
-  constexpr int RTP = (RT + 1) / 2;  // 32-bit words of the RT rows one thread quantises
-  constexpr int RB = R / RT;         // row blocks per tile: a phase-A item is (16-group, row block)
-  static_assert(R % RT == 0, "row blocks tile the tile");
-  static_assert(!(OWN && TAB32), "owned groups convert the 16-bit table once");
-  const int KQ = p.KQ, KE = p.KE, K = KQ + KE;
-  const int G = (KQ - KE) / 16, ngroups = KQ / 16, nunits = KQ / 8, nchunks = K / 64;
-  const CarveT cv = carve_t(R, KQ, KE, RMS, TAB32, S);
-  uint64_t *full = reinterpret_cast<uint64_t *>(smem);
-  float *rcp_lut = reinterpret_cast<float *>(smem + cv.lut), *sf_lut = rcp_lut + 128;
-  const int sfs_bytes = nchunks * 4 * R;
-  uint8_t *arcs = smem + cv.arc;
-  uint8_t *tile = smem + cv.tile;
-  uint8_t *stage = smem + cv.stage;
-  constexpr bool MATX = !RMS && (R == 8 || R == 4 || R == 2);  // transpose with ldmatrix.trans + stmatrix
-  const uint32_t rowbytes = (uint32_t)KQ * 2, rowstride = rowbytes + stage_pad(R);
-  const int tile_bytes = KQ * CB, slot_bytes = R * (int)rowstride;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  float *part = reinterpret_cast<float *>(smem + cv.part), *rstd_s = reinterpret_cast<float *>(smem + cv.rstd);
-  const uint16_t *wtab = reinterpret_cast<const uint16_t *>(smem + cv.wtab);
-
-  // called by every lane of ONE warp with warp-uniform arguments: the address arithmetic stays on the uniform datapath
-  // and one elected lane streams the rows of tile `tile_id` into staging slot s
-  constexpr int IW = (RMS && THREADS / 32 > R) ? R : 0;  // issuing warp: not one of the rmsnorm tree warps
-  auto issue_tile = [&](int s, int tile_id) {
-    const int blk = tile_id / TPB, t = tile_id % TPB;
-    const int r0 = blk * 128 + TileMap<R>::row(t, 0);
-    const int mrows = p.M - r0;
-    int nv = 0;
-#pragma unroll
-    for (int lr = 0; lr < R; ++lr) nv += TileMap<R>::row(0, lr) < mrows ? 1 : 0;
-    const uint8_t *src = reinterpret_cast<const uint8_t *>(p.x) + (int64_t)r0 * rowbytes;
-    uint8_t *dst = stage + (size_t)s * slot_bytes;
-    if (ptx::elect_one()) {
-      ptx::mbar_arrive_expect_tx(&full[s], (uint32_t)nv * rowbytes);
-#pragma unroll
-      for (int lr = 0; lr < R; ++lr)
-        if (TileMap<R>::row(0, lr) < mrows)
-          ptx::bulk_load(dst + (size_t)lr * rowstride, src + (size_t)TileMap<R>::row(0, lr) * rowbytes, rowbytes, &full[s]);
-    }
-    __syncwarp();
-  };
-
-  // ---- one-time setup: barriers, LUTs, gather-offset table ----
-  if (tid == 0) {
-    for (int s = 0; s < S; ++s) ptx::mbar_init(&full[s], 1);
-    ptx::fence_barrier_init();
-  }
-  if (p.M % 128) {  // a ragged last block leaves rows of some slots unwritten: give them defined (zero) content
-    for (int i = tid; i < S * slot_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
-    ptx::fence_proxy_async();
-  }
-  __syncthreads();
-  if (warp == IW) {
-    for (int s = 0; s < S; ++s) {
-      const int tl = blockIdx.x + s * gridDim.x;
-      if (tl < p.num_tiles) issue_tile(s, tl);
-    }
-  }
-  if constexpr (RMS) {  // entries [KQ/16, 512) of the partial sums are never written: the tree reads them as zero
-    for (int i = tid; i < R * 512; i += THREADS) part[i] = 0.0f;
-  }
-  if (tid < 128) {
-    const float sf = e4m3_to_f32(tid < 127 ? tid : 126);
-    sf_lut[tid] = sf;
-    rcp_lut[tid] = __frcp_rn(sf);  // == f32(1.0 / (double)sf) for every E4M3 value (reorder.cu:146)
-  }
-  for (int u = tid; u < nunits; u += THREADS) {
-    const uint4 w4 = __ldg(reinterpret_cast<const uint4 *>(p.idx) + u);
-    const uint32_t ww[4] = {w4.x, w4.y, w4.z, w4.w};
-    uint32_t pos[8];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      pos[2 * i] = (uint32_t)(MATX ? chan_pos_m<R>((int)(ww[i] & 0xffffu)) : chan_pos<R>((int)(ww[i] & 0xffffu)));
-      pos[2 * i + 1] = (uint32_t)(MATX ? chan_pos_m<R>((int)(ww[i] >> 16)) : chan_pos<R>((int)(ww[i] >> 16)));
-    }
-    if constexpr (TAB32) {
-      uint4 *dst = reinterpret_cast<uint4 *>(smem + cv.tab) + 2 * u;
-      dst[0] = make_uint4(pos[0] * CB, pos[1] * CB, pos[2] * CB, pos[3] * CB);
-      dst[1] = make_uint4(pos[4] * CB, pos[5] * CB, pos[6] * CB, pos[7] * CB);
-    } else {
-      reinterpret_cast<uint4 *>(smem + cv.tab)[u] =
-          make_uint4(pos[0] | (pos[1] << 16), pos[2] | (pos[3] << 16), pos[4] | (pos[5] << 16), pos[6] | (pos[7] << 16));
-    }
-    if constexpr (RMS) {  // rmsnorm weight in reordered order
-      uint32_t wv[8];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        wv[2 * i] = __ldg(p.w + (ww[i] & 0xffffu));
-        wv[2 * i + 1] = __ldg(p.w + (ww[i] >> 16));
-      }
-      reinterpret_cast<uint4 *>(smem + cv.wtab)[u] =
-          make_uint4(wv[0] | (wv[1] << 16), wv[2] | (wv[3] << 16), wv[4] | (wv[5] << 16), wv[6] | (wv[7] << 16));
-    }
-  }
-  __syncthreads();
-
-  // gather offsets (bytes into the tile) of the 16 channels of group g
-  auto load_offsets = [&](int g, uint32_t(&off)[16]) {
-    if constexpr (TAB32) {
-      const uint4 *t4 = reinterpret_cast<const uint4 *>(smem + cv.tab) + 4 * g;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) { const uint4 w = t4[q]; off[4 * q] = w.x; off[4 * q + 1] = w.y; off[4 * q + 2] = w.z; off[4 * q + 3] = w.w; }
-    } else {
-      const uint4 *t4 = reinterpret_cast<const uint4 *>(smem + cv.tab) + 2 * g;
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const uint4 w = t4[q];
-        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { off[8 * q + 2 * i] = (ww[i] & 0xffffu) * CB; off[8 * q + 2 * i + 1] = (ww[i] >> 16) * CB; }
-      }
-    }
-  };
-  auto load_w = [&](int g, float(&wf)[16]) {
-    const uint4 *t4 = reinterpret_cast<const uint4 *>(wtab) + 2 * g;
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const uint4 w = t4[q];
-      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) { wf[8 * q + 2 * i] = bf16lo_to_f32(ww[i]); wf[8 * q + 2 * i + 1] = bf16hi_to_f32(ww[i]); }
-    }
-  };
-  auto slots = [&](int g, int &slot_p, int &slot_r) {
-    slot_p = g; slot_r = g;
-    if (g >= G) {
-      const int j = g - G;
-      if constexpr (FLAVOUR == 0) { slot_p = G + 2 * j; slot_r = slot_p + 1; }  // reorder.cu:139,175
-      else { slot_p = G + 4 * (j >> 1) + (j & 1); slot_r = slot_p + 2; }        // reorder.cu:451-463,510-515
-    }
-  };
-
-  uint32_t own_off[OWN ? 16 : 1];
-  if constexpr (OWN) load_offsets(tid / RB < ngroups ? tid / RB : 0, own_off);
-  PrescaleCtx psc = {1.0f, 1.0f, false};
-  if constexpr (PS) {
-    float scale_fp32;
-    psc = make_prescale(__ldg(p.amax), p.prescale_mode == ARCQ_PRESCALE_BF16_DIVISOR, scale_fp32);
-    if (p.scale_out && blockIdx.x == 0 && tid == 0) *p.scale_out = scale_fp32;
-  }
-
-  // scale bytes of one finished tile leave as contiguous 4R-byte runs of the swizzled layout
-  auto copy_out_sf = [&](int buf, int blk, int t) {
-    const uint8_t *sfs = smem + cv.sfs + buf * sfs_bytes;
-    uint8_t *dst0 = p.sf + (int64_t)blk * nchunks * 512 + TileMap<R>::w0(t) * 4;
-    for (int c = tid; c < nchunks; c += THREADS) {
-      uint8_t *dst = dst0 + (int64_t)c * 512;
-      const uint8_t *src = sfs + c * (4 * R);
-      if constexpr (R == 8) {
-        reinterpret_cast<uint4 *>(dst)[0] = reinterpret_cast<const uint4 *>(src)[0];
-        reinterpret_cast<uint4 *>(dst)[1] = reinterpret_cast<const uint4 *>(src)[1];
-      } else if constexpr (R == 4) {
-        *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
-      } else if constexpr (R == 2) {
-        *reinterpret_cast<uint2 *>(dst) = *reinterpret_cast<const uint2 *>(src);
-      } else {
-        *reinterpret_cast<uint32_t *>(dst) = *reinterpret_cast<const uint32_t *>(src);
-      }
-    }
-  };
-
-  int n = 0, prev_blk = 0, prev_t = 0;
-  for (int tile_id = blockIdx.x; tile_id < p.num_tiles; tile_id += gridDim.x, ++n) {
-    const int s = n % S;
-    const int blk = tile_id / TPB, t = tile_id % TPB;
-    const int r0 = blk * 128 + TileMap<R>::row(t, 0);
-    const int mrows = p.M - r0;  // row lr of this tile exists iff row(0, lr) < mrows
-    const uint32_t khalf = (uint32_t)K / 2;
-    uint8_t *qbase = p.q + (int64_t)r0 * khalf;
-    uint8_t *sfs = smem + cv.sfs + (n & 1) * sfs_bytes;
-    ptx::mbar_wait(&full[s], (uint32_t)(n / S) & 1u);
-
-    // ---- transpose the landed rows into the channel-major tile ----
-    {
-      const uint8_t *src = stage + (size_t)s * slot_bytes;
-      auto load_unit = [&](int u, uint4(&in)[R]) {
-#pragma unroll
-        for (int lr = 0; lr < R; ++lr) in[lr] = *reinterpret_cast<const uint4 *>(src + (size_t)lr * rowstride + (size_t)u * 16);
-      };
-      auto store_unit = [&](int u, const uint4(&in)[R]) {
-        if constexpr (R == 1) {
-          reinterpret_cast<uint4 *>(tile)[u] = in[0];
-        } else {
-          const uint32_t u8 = (uint32_t)u * 8, um = (uint32_t)u & (64 / R - 1);  // chan_pos(8u + c) = (8u | c) ^ um
-#pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            uint32_t out[RP];
-#pragma unroll
-            for (int pr = 0; pr < RP; ++pr) {
-              const uint32_t a = (&in[2 * pr].x)[c >> 1], b = (&in[2 * pr + 1].x)[c >> 1];
-              out[pr] = __byte_perm(a, b, (c & 1) ? 0x7632 : 0x5410);
-            }
-            uint8_t *dst = tile + ((u8 | c) ^ um) * CB;
-            if constexpr (R == 8) *reinterpret_cast<uint4 *>(dst) = make_uint4(out[0], out[1], out[2], out[3]);
-            else if constexpr (R == 4) *reinterpret_cast<uint2 *>(dst) = make_uint2(out[0], out[1]);
-            else *reinterpret_cast<uint32_t *>(dst) = out[0];
-          }
-        }
-      };
-      if constexpr (RMS) {
-        // rmsnorm: the reference's thread tt sums channels 8tt..8tt+7 and then 8(bdx+tt)..+7 with one FMA chain
-        // (rmsnorm.cu:113-130) = exactly units tt and bdx+tt of this pass, so the sum of squares rides along
-        const int bdx = KQ / 16;
-        for (int tt = tid; tt < bdx; tt += THREADS) {
-          float acc[R];
-#pragma unroll
-          for (int lr = 0; lr < R; ++lr) acc[lr] = 0.0f;
-#pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint4 in[R];
-            load_unit(half * bdx + tt, in);
-            if constexpr (R % 2 == 0) {  // two rows per packed FFMA2, each row's chain in the reference's order
-#pragma unroll
-              for (int lr = 0; lr < R; lr += 2) {
-                const uint32_t wa[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w};
-                const uint32_t wb[4] = {in[lr + 1].x, in[lr + 1].y, in[lr + 1].z, in[lr + 1].w};
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  fsqacc2(acc[lr], acc[lr + 1], bf16lo_to_f32(wa[i]), bf16lo_to_f32(wb[i]));
-                  fsqacc2(acc[lr], acc[lr + 1], bf16hi_to_f32(wa[i]), bf16hi_to_f32(wb[i]));
-                }
-              }
-            } else {
-#pragma unroll
-              for (int lr = 0; lr < R; ++lr) {
-                const uint32_t w[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w};
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  const float lo = bf16lo_to_f32(w[i]), hi = bf16hi_to_f32(w[i]);
-                  acc[lr] = __fmaf_rn(lo, lo, acc[lr]);
-                  acc[lr] = __fmaf_rn(hi, hi, acc[lr]);
-                }
-              }
-            }
-            store_unit(half * bdx + tt, in);
-          }
-#pragma unroll
-          for (int lr = 0; lr < R; ++lr) part[lr * 512 + tt] = acc[lr];
-        }
-      } else if constexpr (MATX) {
-        // a warp step moves 256/R channels x R rows: matrix m = channels [CW k + MC m, +MC); its 8 rows are the R tile
-        // rows of each of the 8/R 8-channel blocks; transposed, row i of the stored matrix is the 16 bytes
-        // {chunk of channel 8 hb + i : hb} = chan_pos_m.  k = warp + NW it keeps the swizzle terms per-warp constants.
-        constexpr int NW = THREADS / 32, CW = 256 / R, MC = CW / 4, HB = R == 8 ? 1 : 8 / R;
-        static_assert(NW % 8 == 0, "swizzle terms must not depend on the iteration");
-        const int m = lane >> 3, r = lane & 7;
-        const uint32_t src_s = ptx::smem_u32(src), tile_s = ptx::smem_u32(tile);
-        auto ld_addr = [&](int k) {
-          const int hsw = (k >> 1) & (HB - 1);
-          return src_s + (uint32_t)(r % R) * rowstride + (uint32_t)(k * CW + m * MC + 8 * ((r / R) ^ hsw)) * 2;
-        };
-        auto st_addr = [&](int k) {
-          const int b = 4 * k + m;
-          return tile_s + (uint32_t)((b * 8 + (r ^ (b & 7))) * 16);
-        };
-        const int nch = ARCQ_DBG(p, 1) ? 0 : KQ / CW;
-        uint32_t la = ld_addr(warp), sa = st_addr(warp);
-#pragma unroll 4
-        for (int k = warp; k < nch; k += NW) {
-          uint32_t f[4];
-          ptx::ldsm_x4_t(la, f);
-          ptx::stsm_x4(sa, f);
-          la += NW * CW * 2;
-          sa += NW * CW * CB;
-        }
-        if constexpr (R == 2) {  // KQ = 64 (mod 128): the last half step has two matrices
-          if ((KQ & 64) && warp == (KQ / CW) % NW && !ARCQ_DBG(p, 1)) {
-            uint32_t f[4];
-            ptx::ldsm_x2_t(ld_addr(KQ / CW), f);
-            ptx::stsm_x2(st_addr(KQ / CW), f);
-          }
-        }
-      } else {
-        for (int u = tid; u < (ARCQ_DBG(p, 1) ? 0 : nunits); u += THREADS) {
-          uint4 in[R];
-          load_unit(u, in);
-          store_unit(u, in);
-        }
-      }
-    }
-    __syncthreads();
-    if (warp == IW) {  // slot s has been read by everyone: refill it with the tile S steps ahead
-      const int tl = tile_id + S * gridDim.x;
-      if (tl < p.num_tiles) issue_tile(s, tl);
-    }
-    // every thread has finished phase B of the previous tile (it passed the barrier above): its scale bytes are complete
-    if (n > 0) copy_out_sf((n - 1) & 1, prev_blk, prev_t);
-
-    // ---- rmsnorm: the reference's reduction tree over the per-thread partial sums (rmsnorm.cu:131-157) ----
-    if constexpr (RMS) {
-      if (warp < R) {  // one warp replays the reference's tree for one row (rmsnorm.cu:131-154)
-        // strides 256, 128, 64 and the final s[t] + s[t+32] pair element t with t + 32 k: all in the same lane, so the
-        // whole shared-memory tree is 15 register adds per lane in the reference's association order
-        const float *sp = part + warp * 512;
-        float a[16];
-#pragma unroll
-        for (int k = 0; k < 16; ++k) a[k] = sp[lane + 32 * k];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) a[k] = __fadd_rn(a[k], a[k + 8]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) a[k] = __fadd_rn(a[k], a[k + 4]);
-#pragma unroll
-        for (int k = 0; k < 2; ++k) a[k] = __fadd_rn(a[k], a[k + 2]);
-        float v = __fadd_rn(a[0], a[1]);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
-        if (lane == 0) rstd_s[warp] = rsqrtf(__fadd_rn(__fdiv_rn(v, (float)KQ), p.eps));  // :157
-      }
-      __syncthreads();
-    }
-
-    // ---- phase A: permuted gather + primary quantisation; one item = (16-group, block of RT rows) per thread per step ----
-    for (int item = tid; item < ngroups * RB; item += THREADS) {
-      const int g = item / RB, rb = item % RB;
-      uint32_t v[16][RTP];
-      if (ARCQ_DBG(p, 2)) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-#pragma unroll
-          for (int w = 0; w < RTP; ++w) v[i][w] = (uint32_t)g * 0x9e3779b9u + i;
-      } else if constexpr (OWN) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + own_off[i] + rb * (2 * RT), v[i]);
-      } else {
-        uint32_t off[16];
-        load_offsets(g, off);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + off[i] + rb * (2 * RT), v[i]);
-      }
-      if constexpr (PS) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-#pragma unroll
-          for (int w = 0; w < RTP; ++w) v[i][w] = prescale_bf16x2(v[i][w], psc);
-      }
-      float wf[RMS ? 16 : 1];
-      if constexpr (RMS) load_w(g, wf);
-      int slot_p, slot_r;
-      slots(g, slot_p, slot_r);
-      uint8_t *sfp = sfs + (slot_p >> 2) * (4 * R) + (slot_p & 3) + 4 * RT * rb;
-      const int dslot = slot_r - slot_p;
-      const bool arc = g >= G;
-      const int drb = TileMap<R>::row(0, rb * RT);  // row(0, rb*RT + lr) = row(0, rb*RT) + row(0, lr) for every TileMap
-      uint8_t *qg = qbase + 8 * slot_p + (uint32_t)drb * khalf;
-      const int mr = mrows - drb;
-      // store one quantised row: scale byte, codes, and (activations) the residual work item of an ARC group
-      auto emit_row = [&](int lr, uint32_t sfb, uint32_t c_lo, uint32_t c_hi, float sc, const uint32_t(&xb)[8]) {
-        sfp[4 * lr] = (uint8_t)sfb;
-        if (IS_W && arc) sfp[4 * lr + ((dslot >> 2) * (4 * R) + (dslot & 3))] = (uint8_t)sfb;  // reorder.cu:307-316
-        if (!IS_W && arc) {  // hand the residual work of this (group,row) to phase B: values, codes, subtrahend scale
-#ifdef ARCQ_STASH_LRMAJOR
-          uint4 *a = reinterpret_cast<uint4 *>(arcs + (rb * RT + lr) * ((KE / 16) * 48 + 16) + (g - G) * 48);
-#else
-          uint4 *a = reinterpret_cast<uint4 *>(arcs + ((g - G) * R + rb * RT + lr) * 48);
-#endif
-          a[0] = make_uint4(xb[0], xb[1], xb[2], xb[3]);
-          a[1] = make_uint4(xb[4], xb[5], xb[6], xb[7]);
-          // 16-wide: rounded scale (reorder.cu:157); 32-wide: unrounded (reorder.cu:474)
-          a[2] = make_uint4(c_lo, c_hi, __float_as_uint(FLAVOUR == 0 ? sf_lut[sfb] : sc), 0u);
-        }
-        uint8_t *qp = qg + TileMap<R>::row(0, lr) * khalf;
-        if (TileMap<R>::row(0, lr) < mr) {
-          __stcs(reinterpret_cast<uint2 *>(qp), make_uint2(c_lo, c_hi));
-          if (IS_W && arc) __stcs(reinterpret_cast<uint2 *>(qp + 8 * dslot), make_uint2(c_lo, c_hi));
-        }
-      };
-      // two rows per step with packed FP32 multiplies: measured faster for the rmsnorm variant (-6..9 %) and for 2-row
-      // items (-7 %), slower for plain 4-row items (+17 %)  (profiles/r1_quant_packed_ab.log)
-      constexpr bool kPacked2 = (RT % 2 == 0) && (RMS || RT == 2);
-      if constexpr (kPacked2) {
-        // two rows per step: the chunk word w2 holds rows 2 w2 (low halves) and 2 w2 + 1 (high halves) of every channel
-#pragma unroll
-        for (int w2 = 0; w2 < RT / 2; ++w2) {
-          uint32_t pv[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) pv[i] = v[i][w2];
-          if constexpr (RMS) normalise16x2(pv, wf, rstd_s[rb * RT + 2 * w2], rstd_s[rb * RT + 2 * w2 + 1]);
-          uint32_t sfb[2], c[2][2];
-          float sc[2];
-          quant16x2(pv, rcp_lut, sfb, c, sc);
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            uint32_t xb[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(pv[2 * i], pv[2 * i + 1], h ? 0x7632 : 0x5410);
-            emit_row(2 * w2 + h, sfb[h], c[h][0], c[h][1], sc[h], xb);
-          }
-        }
-      } else {
-#pragma unroll
-        for (int lr = 0; lr < RT; ++lr) {
-          float x[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            x[i] = (lr & 1) ? bf16hi_to_f32(v[i][lr >> 1]) : bf16lo_to_f32(v[i][lr >> 1]);
-            if constexpr (RMS)  // rmsnorm.cu:165-171: bf16((x * w) * rstd), left to right
-              x[i] = bf16lo_to_f32(f32_to_bf16_bits(__fmul_rn(__fmul_rn(x[i], wf[i]), rstd_s[rb * RT + lr])));
-          }
-          uint32_t c_lo, c_hi;
-          float sc;
-          uint32_t sfb;
-          if (ARCQ_DBG(p, 4)) { sfb = __float_as_uint(x[0]) >> 24; c_lo = __float_as_uint(x[1]); c_hi = __float_as_uint(x[15]); sc = x[2]; }
-          else sfb = quant16(x, rcp_lut, c_lo, c_hi, sc);
-          uint32_t xb[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) xb[i] = __byte_perm(__float_as_uint(x[2 * i]), __float_as_uint(x[2 * i + 1]), 0x7632);
-          emit_row(lr, sfb, c_lo, c_hi, sc, xb);
-        }
-      }
-      if constexpr (OWN) break;  // THREADS >= items: one item per thread, its offsets stay in registers
-    }
-
-    // ---- phase B: ARC residuals, one (group, row) item per thread per step, from the stash of phase A ----
-    if constexpr (!IS_W) {
-      __syncthreads();  // stash complete; also: nobody reads the tile any more (the next transpose may overwrite it)
-#ifndef ARCQ_PHASEB_QUAD  // one thread per (group,row) item; the 4-lanes-per-item variant below measured 5 % slower (r1l_quant.log)
-      const int nitems = ARCQ_DBG(p, 8) ? 0 : (KE / 16) * R;
-      for (int item = tid; item < nitems; item += THREADS) {
-#ifdef ARCQ_STASH_LRMAJOR
-        const int nper = KE / 16, lr = item / nper, g = G + item % nper;
-        const uint4 *a = reinterpret_cast<const uint4 *>(arcs + lr * (nper * 48 + 16) + (g - G) * 48);
-#else
-        const int g = G + item / R, lr = item % R;
-        const uint4 *a = reinterpret_cast<const uint4 *>(arcs + item * 48);
-#endif
-        const uint4 x0 = a[0], x1 = a[1], cs = a[2];
-        const uint32_t xb[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-        float x[16];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { x[2 * i] = bf16lo_to_f32(xb[i]); x[2 * i + 1] = bf16hi_to_f32(xb[i]); }
-        uint32_t r_lo, r_hi;
-        const uint32_t rsfb = residual16(x, cs.x, cs.y, __uint_as_float(cs.z), rcp_lut, r_lo, r_hi);
-        int slot_p, slot_r;
-        slots(g, slot_p, slot_r);
-        sfs[(slot_r >> 2) * (4 * R) + 4 * lr + (slot_r & 3)] = (uint8_t)rsfb;
-        const int dr = TileMap<R>::row(0, lr);
-        if (dr < mrows) __stcs(reinterpret_cast<uint2 *>(qbase + (uint32_t)dr * khalf + 8 * slot_r), make_uint2(r_lo, r_hi));
-      }
-#else
-      // four lanes share one (group,row) item: each requantises 4 of its 16 residuals, the quad reduces amax
-      const int nitems = ARCQ_DBG(p, 8) ? 0 : (KE / 16) * R;
-      const int sub = lane & 3;
-      for (int base = warp * 8; base < nitems; base += (THREADS / 32) * 8) {  // warp-uniform: shuffles below
-        const int it0 = base + (lane >> 2);
-        const bool active = it0 < nitems;
-        const int item = active ? it0 : nitems - 1;
-        const int g = G + item / R, lr = item % R;
-        const uint8_t *a = arcs + item * 48;
-        const uint2 xw = reinterpret_cast<const uint2 *>(a)[sub];     // x[4 sub .. 4 sub + 3] as bf16
-        const uint4 cs = reinterpret_cast<const uint4 *>(a)[2];      // code words, subtrahend scale
-        const uint32_t nib = ((sub < 2 ? cs.x : cs.y) >> (16 * (sub & 1))) & 0xffffu;
-        const float subs = __uint_as_float(cs.z);
-        const float x4[4] = {bf16lo_to_f32(xw.x), bf16hi_to_f32(xw.x), bf16lo_to_f32(xw.y), bf16hi_to_f32(xw.y)};
-        float e[4];
-        float amax = 0.0f;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {  // e = bf16(x - deq(code) * scale) (reorder.cu:157-160 / :474)
-          e[j] = bf16lo_to_f32(f32_to_bf16_bits(__fmaf_rn(-e2m1_to_f32((nib >> (4 * j)) & 0xfu), subs, x4[j])));
-          amax = fmaxf(amax, fabsf(e[j]));
-        }
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-        const float sc2 = fmaxf(kScaleEps, fminf(kFp8Max, div6(amax)));
-        const uint32_t rsfb = f32_to_e4m3(sc2);
-        const float r = rcp_lut[rsfb];
-        const uint32_t my16 = f32x4_to_e2m1(__fmul_rn(e[0], r), __fmul_rn(e[1], r), __fmul_rn(e[2], r), __fmul_rn(e[3], r));
-        const uint32_t nb16 = __shfl_xor_sync(0xffffffffu, my16, 1);
-        const uint32_t word = (sub & 1) ? (nb16 | (my16 << 16)) : (my16 | (nb16 << 16));  // lanes 0,1: elements 0-7; 2,3: 8-15
-        const uint32_t other = __shfl_xor_sync(0xffffffffu, word, 2);
-        if (active && sub == 0) {
-          int slot_p, slot_r;
-          slots(g, slot_p, slot_r);
-          sfs[(slot_r >> 2) * (4 * R) + 4 * lr + (slot_r & 3)] = (uint8_t)rsfb;
-          const int dr = TileMap<R>::row(0, lr);
-          if (dr < mrows) __stcs(reinterpret_cast<uint2 *>(qbase + (uint32_t)dr * khalf + 8 * slot_r), make_uint2(word, other));
-        }
-      }
-#endif
-    } else {
-      __syncthreads();
-    }
-    prev_blk = blk; prev_t = t;
-  }
-  if (n > 0) {  // scale bytes of the last tile
-    __syncthreads();
-    copy_out_sf((n - 1) & 1, prev_blk, prev_t);
-  }
-}
-
-// ---- host side ------------------------------------------------------------------------------
-
-constexpr int kSmemPerSm = 227 * 1024;
-
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS>
-int launch(const QuantParams &p0, int S, cudaStream_t stream) {
-  QuantParams p = p0;
-#ifdef ARCQ_EXPERIMENT
-  if (const char *e = getenv("ARCQ_QUANT_DEBUG")) p.debug = atoi(e);
-#endif
-  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB, PS>;
-  const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S).total;
-  static SmemAttrCache attr_cache = {};  // per instantiation, per device
-  if (int rc = ensure_dynamic_smem(kern, smem, attr_cache)) return rc;
-  const int sms = sm_count();
-  if (sms <= 0) return ARCQ_ECUDA;
-  p.num_tiles = (int)(((int64_t)p.M + 127) / 128) * (128 / R);
-  const int grid = p.num_tiles < sms * MINB ? p.num_tiles : sms * MINB;
-  kern<<<grid, THREADS, smem, stream>>>(p, S);
-  ARCQ_CUDA_TRY(cudaGetLastError());
-  count_launch();
-  return ARCQ_OK;
-}
-
-template <int R, int RT, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS, bool PS = false>
-int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t st) {
-  if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB, PS>(p, S, st);
-  if (tab32) return launch<R, RT, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB, PS>(p, S, st);
-  return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB, PS>(p, S, st);
-}
-
-template <int R, int RT, int THREADS, int MINB>
-int launch_kind(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st) {
-  if (rms) return launch_tab<R, RT, THREADS, MINB, 0, false, true>(p, S, tab32, own, st);
-  if (is_w) return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, true, false>(p, S, tab32, own, st)
-                                              : launch_tab<R, RT, THREADS, MINB, 0, true, false>(p, S, tab32, own, st);
-  if (p.amax)
-    return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false, true>(p, S, tab32, own, st)
-                                      : launch_tab<R, RT, THREADS, MINB, 0, false, false, true>(p, S, tab32, own, st);
-  return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false>(p, S, tab32, own, st)
-                                    : launch_tab<R, RT, THREADS, MINB, 0, false, false>(p, S, tab32, own, st);
-}
-
 struct Cfg { int R, threads, minb, S, RT; };
 
 }  // namespace
+
+// one translation unit per tile organisation (quant_tma_cfg.cu compiled with -DARCQ_CFG_*; see build.py)
+#define ARCQ_CFG_DECL(RR, RTT, TH, MB) \
+  int launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st);
+ARCQ_CFG_DECL(4, 4, 256, 2) ARCQ_CFG_DECL(4, 4, 512, 1) ARCQ_CFG_DECL(2, 2, 256, 2) ARCQ_CFG_DECL(2, 2, 512, 1) ARCQ_CFG_DECL(1, 1, 512, 1)
+ARCQ_CFG_DECL(8, 8, 512, 1) ARCQ_CFG_DECL(8, 4, 512, 1)
+#undef ARCQ_CFG_DECL
 
 int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cudaStream_t stream) {
   if (p.KQ % 64 || p.KE % 64) return ARCQ_ENOSUP;  // 4-slot scale chunks must not straddle the plain/ARC boundary
@@ -617,12 +34,13 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     const int *q = options().quant_tile;
     if (q[0] > 0) c = Cfg{q[0], q[1], q[4], q[2], q[3]};
   }
+  const bool want_plan = p.plan != nullptr && !rms && !is_w;
   if (c.R == 0) {
     for (const Cfg &k : cands) {
       if (rms && k.threads < 32 * k.R) continue;
       if (k.R == 8 && ngroups * (k.R / k.RT) > k.threads) continue;  // only with one owned item per thread
       if (k.R == 4 && k.threads == 256 && ngroups > 256) continue;   // two passes per tile: the wide CTA owns its items
-      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
+      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S, want_plan && plan_usable(k.R, p.KQ)).total + 1024;
       if (need * k.minb > kSmemPerSm) continue;
       if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;
       c = k;
@@ -631,11 +49,14 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     if (c.R == 0) return ARCQ_ENOSUP;
   }
   own = ngroups * (c.R / c.RT) <= c.threads;
-  tab32 = !own && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
-  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
+  QuantParams pp = p;
+  const bool planned = want_plan && plan_usable(c.R, p.KQ);
+  pp.plan = planned ? p.plan + (int64_t)plan_section(c.R) * p.KQ : nullptr;   // this tile height's section
+  tab32 = !own && !planned && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
+  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
 #define ARCQ_T(RR, RTT, TH, MB) \
   if (c.R == RR && c.RT == RTT && c.threads == TH && c.minb == MB) \
-    return launch_kind<RR, RTT, TH, MB>(p, flavour, is_w, rms, c.S, tab32, own, stream);
+    return launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(pp, flavour, is_w, rms, c.S, tab32, own, stream);
   ARCQ_T(4, 4, 256, 2) ARCQ_T(4, 4, 512, 1) ARCQ_T(2, 2, 256, 2) ARCQ_T(2, 2, 512, 1) ARCQ_T(1, 1, 512, 1)
   ARCQ_T(8, 8, 512, 1) ARCQ_T(8, 4, 512, 1)
 #undef ARCQ_T

@@ -109,6 +109,24 @@ int arcq_quantize_x_scaled(const void *x, int64_t M, int KQ, const int16_t *idx,
                            const float *amax_dev, int prescale_mode, void *qx, void *sfx, float *scale_out,
                            void *stream);
 
+/* Conflict-free shared-memory placement for one reorder_index ("plan"; csrc/plan.cu) -- computed ONCE per layer on the
+ * host (index arithmetic only, O(KQ log 32)), uploaded by the caller, and passed to arcq_quantize_x_ex.  It removes the
+ * bank conflicts of the permuted gather (reorder.cu:115-118) for any permutation.  A plan is only ever an optimisation:
+ * the kernel requires it to be a bijection (arcq_plan_build guarantees it) but derives its gather offsets from
+ * plan[reorder_index[k]] itself, so a plan built for a DIFFERENT index still gives correct bytes.
+ *   arcq_plan_entries(KQ)  number of uint16 entries (3 * KQ: sections for 8-, 4- and 2-row tiles);
+ *   arcq_plan_build        host pointers; ARCQ_EINVAL if idx is not a permutation of [0, KQ);
+ *   arcq_plan_max_conflict worst bank-slot multiplicity of any wavefront under a plan for tile height R (1 = none). */
+int64_t arcq_plan_entries(int KQ);
+int arcq_plan_build(const int16_t *idx_host, int KQ, uint16_t *plan_host);
+int arcq_plan_max_conflict(const int16_t *idx_host, int KQ, int R, const uint16_t *plan_host);
+
+/* arcq_quantize_x with the optional extras: plan_dev (nullable, device copy of a plan) and the fused pre-scale
+ * (amax_dev nullable; prescale_mode / scale_out as in arcq_quantize_x_scaled). */
+int arcq_quantize_x_ex(const void *x, int64_t M, int KQ, const int16_t *idx, int KE, int flavour,
+                       const uint16_t *plan_dev, const float *amax_dev, int prescale_mode, void *qx,
+                       void *sfx, float *scale_out, void *stream);
+
 /* name = value override of a shape-driven kernel choice ("" = back to the default).  Every choice computes the same
  * result; the parity tests force each tile organisation through this.  Options: "quant_tile" = "R,threads,S,RT,CTAs/SM",
  * "quant_family" = 3 | 1, "gemm_pair" = 0 | 1, "gemm_bn" = 128 | 256, "gemm_splitk" = 0 | 2 | 4 | 8.  The product

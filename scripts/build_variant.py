@@ -6,9 +6,10 @@ name, defs = sys.argv[1], sys.argv[2:]
 objdir = os.path.join(os.path.dirname(b.LIB), "build", "variant_" + name)
 os.makedirs(objdir, exist_ok=True)
 procs, objs = [], []
-for src in b.SOURCES:
-    obj = os.path.join(objdir, src.replace(".cu", ".o"))
-    procs.append(subprocess.Popen([b._nvcc()] + b.NVCC_FLAGS + defs + ["-c", os.path.join(b.CSRC, src), "-o", obj]))
+for entry in b.SOURCES:
+    src, extra, oname = entry if isinstance(entry, tuple) else (entry, [], entry.replace(".cu", ".o"))
+    obj = os.path.join(objdir, oname)
+    procs.append(subprocess.Popen([b._nvcc()] + b.NVCC_FLAGS + extra + defs + ["-c", os.path.join(b.CSRC, src), "-o", obj]))
     objs.append(obj)
 assert all(p.wait() == 0 for p in procs)
 out = os.path.join(os.path.dirname(b.LIB), "libarcq_%s.so" % name)

@@ -136,14 +136,15 @@ def test_swiglu_math_matches_torch_exhaustively():
     A = one-hot codes so that acc = g exactly is impractical; instead compare on the identity-weight trick below."""
     from arcquant_b200 import agemm
     # K = 64, codes 1.0 in one position: acc[m, n] = a[m, k0] * b[n, k0]; with b = 1 and scales 1 the accumulator IS a[m].
-    # e2m1 has 15 values, E4M3 scales 127: a[m] * sfa sweeps 15 * 127 distinct gate values, up = 1.
+    # e2m1 has 15 values, E4M3 126 finite scales: a[m] * sfa sweeps 15 * 126 distinct gate values (|g| up to 2688:
+    # saturated both ways), up = gate.
     M, N, K = 128 * 15, 256, 64
     qa = torch.zeros((M, K // 2), dtype=torch.uint8, device="cuda")
     code = (torch.arange(M, device="cuda") // 128) + 1          # 1..15 (skips +0)
     qa[:, 0] = code.to(torch.uint8)
     sfa = torch.zeros((agemm.sf_bytes(M, K),), dtype=torch.uint8, device="cuda")
     rows = torch.arange(M, device="cuda")
-    sfa[T.sf_offsets(rows, K)[:, 0]] = (rows % 127).to(torch.uint8) + 1   # E4M3 bytes 1..127 on group 0
+    sfa[T.sf_offsets(rows, K)[:, 0]] = (rows % 126).to(torch.uint8) + 1   # E4M3 bytes 1..126 on group 0 (0x7f is NaN)
     qb = torch.zeros((N, K // 2), dtype=torch.uint8, device="cuda")
     qb[:, 0] = 0x02                                               # b[n, 0] = 1.0
     sfb = torch.full((agemm.sf_bytes(N, K),), 0x38, dtype=torch.uint8, device="cuda")   # 1.0

@@ -85,8 +85,10 @@ def test_scaled_quantise_equals_torch_prescale_then_quantise(M, KQ, KE, mag):
         assert nq == 0 and ns == 0, "M=%d KQ=%d KE=%d mode=%d: %d code bytes, %d scale bytes differ" % (M, KQ, KE, mode, nq, ns)
     q, sf, scale = agemm.reorder_quantize_x_scaled(xd, idxd, KE, mode=agemm.PRESCALE_FP32)
     # and the whole chain against the CPU oracle fed with torch's (CPU) pre-scaled tensor
-    s_cpu = torch.max(x.abs()).float() / (448.0 * 6.0)
-    q_o, sf_o = O.quantize_x(bits((x / s_cpu).to(torch.bfloat16)), idx.numpy(), KE)
+    # CUDA torch computes `tensor / python_scalar` as tensor * (1 / scalar) in fp32 (CPU torch divides): restate that
+    s_cpu = torch.max(x.abs()).float() * torch.tensor(1.0, dtype=torch.float32).div(2688.0)
+    assert float(s_cpu) == float(scale)
+    q_o, sf_o = O.quantize_x(bits((x.float() / s_cpu).to(torch.bfloat16)), idx.numpy(), KE)
     offn = O.sf_valid_offsets(M, KQ + KE)
     assert np.array_equal(q.cpu().numpy(), q_o) and np.array_equal(sf.cpu().numpy()[offn], sf_o[offn])
 

