@@ -44,17 +44,19 @@ def test_planned_kernels_match_oracle(arcq_option, knob, M, KQ, KE):
         q2, sf2 = agemm.reorder_quantize_x_planned(xd, idxd, KE, plan.cuda())
         other = torch.randperm(KQ, generator=torch.Generator().manual_seed(1)).to(torch.int16)
         q3, sf3 = agemm.reorder_quantize_x_planned(xd, idxd, KE, agemm.plan_build(other).cuda())   # stale plan: still correct
-        q5, sf5, _ = agemm.reorder_quantize_x_scaled(xd, idxd, KE, amax=torch.tensor([2688.0], device="cuda"))  # scale exactly 1
+        am = torch.tensor([1777.0], device="cuda")
+        q5, sf5, _ = agemm.reorder_quantize_x_scaled(xd, idxd, KE, amax=am)   # planned + fused pre-scale
         agemm.use_plans(False)
         q4, sf4 = agemm.reorder_quantize_x(xd, idxd, KE)                  # arithmetic placement
+        q6, sf6, _ = agemm.reorder_quantize_x_scaled(xd, idxd, KE, amax=am)   # (pinned to torch by tests/test_gpu_prescale.py)
     finally:
         agemm.use_plans(True)
     torch.cuda.synchronize()
     K = KQ + KE
     for tag, (q, sf) in {"cached plan": (q1, sf1), "explicit plan": (q2, sf2), "stale plan": (q3, sf3), "no plan": (q4, sf4)}.items():
         assert _same(q, sf, q_ref, sf_ref, M, K) == 0, "%s (%s M=%d KQ=%d KE=%d)" % (tag, knob, M, KQ, KE)
-    # x / 1.0 is x: the pre-scaled planned kernel on an already-scaled tensor
-    assert _same(q5, sf5, q_ref, sf_ref, M, K) == 0, "planned + pre-scale"
+    off = torch.from_numpy(O.sf_valid_offsets(M, K)).cuda()
+    assert torch.equal(q5, q6) and torch.equal(sf5[off], sf6[off]), "planned + pre-scale differs from unplanned + pre-scale"
 
 
 @pytest.mark.parametrize("M,KQ,KE", [(8192, 4096, 256), (4096 + 77, 14336, 512), (2500, 8192, 512), (3000, 3584, 256)])
