@@ -40,7 +40,9 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
       if (rms && k.threads < 32 * k.R) continue;
       if (k.R == 8 && ngroups * (k.R / k.RT) > k.threads) continue;  // only with one owned item per thread
       if (k.R == 4 && k.threads == 256 && ngroups > 256) continue;   // two passes per tile: the wide CTA owns its items
-      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S, want_plan && plan_usable(k.R, p.KQ)).total + 1024;
+      // a placement plan is an extra: the tile organisation is chosen as if there were none, and the plan is used only
+      // if it still fits next to it (below); it must never push the choice to a smaller tile
+      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
       if (need * k.minb > kSmemPerSm) continue;
       if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;
       c = k;
@@ -50,7 +52,11 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   }
   own = ngroups * (c.R / c.RT) <= c.threads;
   QuantParams pp = p;
-  const bool planned = want_plan && plan_usable(c.R, p.KQ);
+  bool planned = want_plan && plan_usable(c.R, p.KQ);
+  if (planned && (carve_t(c.R, p.KQ, p.KE, rms, false, c.S, true).total + 1024) * c.minb > kSmemPerSm) {
+    if (c.S > 1 && (carve_t(c.R, p.KQ, p.KE, rms, false, 1, true).total + 1024) * c.minb <= kSmemPerSm) c.S = 1;  // trade the second staging slot
+    else planned = false;
+  }
   pp.plan = planned ? p.plan + (int64_t)plan_section(c.R) * p.KQ : nullptr;   // this tile height's section
   tab32 = !own && !planned && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
   if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;

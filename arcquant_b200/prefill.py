@@ -73,7 +73,10 @@ class ArcDecoderLayer(torch.nn.Module):
     per-column scales, gate/up as ONE GEMM whose epilogue writes bf16(silu(gate)) * up, per-tensor pre-scales inside the
     quantise kernels.  fused=False: the reference's launch structure (7 GEMMs, SiLU*up and the pre-scales in torch)."""
 
-    def __init__(self, cfg: PrefillConfig, dev, gen, world=1, rank=0, group=None, keep_ref=False, fused=True):
+    def __init__(self, cfg: PrefillConfig, dev, gen, world=1, rank=0, group=None, keep_ref=False, fused=True, calib=None,
+                 layer_idx=0):
+        """calib: (reorder_index, select_nums) dicts in the reference's on-disk schema (arcquant_b200/calib.py); without it
+        every quantise input gets a random permutation and the configured select_num."""
         super().__init__()
         from . import agemm
         self.ref = {} if keep_ref else None  # bf16 weights / biases kept only for the parity test
@@ -86,6 +89,13 @@ class ArcDecoderLayer(torch.nn.Module):
         self.fused = bool(fused) and (H // world) % 128 == 0 and (I // world) % 128 == 0
         self.idx_h1, self.idx_h2 = _rand_index(H, dev, gen), _rand_index(H, dev, gen)  # inputs of qkv and of gate/up
         idx_o, idx_d = _rand_index(H, dev, gen), _rand_index(I, dev, gen)
+        ke_qkv = ke_gu = ke_o = cfg.ke_hidden
+        ke_d = cfg.ke_intermediate
+        if calib is not None:
+            from . import calib as C
+            e = C.layer_entries(calib[0], calib[1], layer_idx, dev)
+            (self.idx_h1, ke_qkv), (idx_o, ke_o), (self.idx_h2, ke_gu), (idx_d, ke_d) = e["qkv"], e["o"], e["gate_up"], e["down"]
+        self.ke_qkv, self.ke_gu = ke_qkv, ke_gu
         self.norm1 = torch.ones(H, dtype=torch.bfloat16, device=dev)
         self.norm2 = torch.ones(H, dtype=torch.bfloat16, device=dev)
 
@@ -104,13 +114,13 @@ class ArcDecoderLayer(torch.nn.Module):
         def col(name, n, k, idx, ke, b=None):
             return tp.ColumnParallelQLinear(weight(name, n, k, b), idx, ke, world, rank, b, flavour=F16)
 
-        self.q = col("q", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
-        self.k = col("k", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
-        self.v = col("v", H, H, self.idx_h1, cfg.ke_hidden, bias(H))
-        self.gate = col("gate", I, H, self.idx_h2, cfg.ke_hidden)
-        self.up = col("up", I, H, self.idx_h2, cfg.ke_hidden)
-        self.o = tp.RowParallelQLinear(weight("o", H, H), idx_o, cfg.ke_hidden, world, rank, group=group)
-        self.down = tp.RowParallelQLinear(weight("down", H, I), idx_d, cfg.ke_intermediate, world, rank, group=group)
+        self.q = col("q", H, H, self.idx_h1, ke_qkv, bias(H))
+        self.k = col("k", H, H, self.idx_h1, ke_qkv, bias(H))
+        self.v = col("v", H, H, self.idx_h1, ke_qkv, bias(H))
+        self.gate = col("gate", I, H, self.idx_h2, ke_gu)
+        self.up = col("up", I, H, self.idx_h2, ke_gu)
+        self.o = tp.RowParallelQLinear(weight("o", H, H), idx_o, ke_o, world, rank, group=group)
+        self.down = tp.RowParallelQLinear(weight("down", H, I), idx_d, ke_d, world, rank, group=group)
         if self.fused:
             self.qkv_w = agemm.fuse_weights([(l.W, l.scale_w, l.scale) for l in (self.q, self.k, self.v)])
             self.qkv_bias = torch.cat([l.bias for l in (self.q, self.k, self.v)]) if cfg.qkv_bias else None
@@ -131,13 +141,13 @@ class ArcDecoderLayer(torch.nn.Module):
         B, S, H = h.shape
         x2d = h.reshape(B * S, H)
         if self.fused:
-            qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm1, self.cfg.eps, self.idx_h1, self.cfg.ke_hidden)
+            qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm1, self.cfg.eps, self.idx_h1, self.ke_qkv)
             qkv = ag.matmul(qx, self.qkv_w[0], sfx, self.qkv_w[1], self.one, col_scale=self.qkv_w[2])
             if self.qkv_bias is not None:
                 qkv = qkv + self.qkv_bias
             q, k, v = qkv.split(H // self.world, dim=1)
         else:
-            q, k, v = self._norm_linears(x2d, self.norm1, self.idx_h1, self.cfg.ke_hidden, (self.q, self.k, self.v))
+            q, k, v = self._norm_linears(x2d, self.norm1, self.idx_h1, self.ke_qkv, (self.q, self.k, self.v))
         shp = (B, S, self.local_heads, self.head_dim)
         q, k, v = (t.reshape(shp).transpose(1, 2) for t in (q, k, v))
         q, k = _rope(q, k)
@@ -145,10 +155,10 @@ class ArcDecoderLayer(torch.nn.Module):
         h = h + self._row(self.o, a).view(B, S, H)              # quantise (local permutation + ARC) -> GEMM -> all-reduce
         x2d = h.reshape(B * S, H)
         if self.fused:
-            qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm2, self.cfg.eps, self.idx_h2, self.cfg.ke_hidden)
+            qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm2, self.cfg.eps, self.idx_h2, self.ke_gu)
             m = ag.matmul(qx, self.gu_w[0], sfx, self.gu_w[1], self.one, col_scale=self.gu_w[2], epilogue=ag.EPILOGUE_SWIGLU)
         else:
-            g, u = self._norm_linears(x2d, self.norm2, self.idx_h2, self.cfg.ke_hidden, (self.gate, self.up))
+            g, u = self._norm_linears(x2d, self.norm2, self.idx_h2, self.ke_gu, (self.gate, self.up))
             m = (F.silu(g) * u).contiguous()
         return h + self._row(self.down, m).view(B, S, H)
 
@@ -180,12 +190,12 @@ def reference_layer_forward(layer: "ArcDecoderLayer", h: torch.Tensor) -> torch.
 
 
 class ArcPrefillModel(torch.nn.Module):
-    def __init__(self, cfg: PrefillConfig, device, seed=0, world=1, rank=0, group=None, keep_ref=False, fused=True):
+    def __init__(self, cfg: PrefillConfig, device, seed=0, world=1, rank=0, group=None, keep_ref=False, fused=True, calib=None):
         super().__init__()
         gen = torch.Generator(device=device).manual_seed(seed)  # same seed on every rank: shards of the same weights
         self.cfg = cfg
-        self.layers = torch.nn.ModuleList([ArcDecoderLayer(cfg, device, gen, world, rank, group, keep_ref, fused)
-                                           for _ in range(cfg.layers)])
+        self.layers = torch.nn.ModuleList([ArcDecoderLayer(cfg, device, gen, world, rank, group, keep_ref, fused, calib, i)
+                                           for i in range(cfg.layers)])
 
     @torch.no_grad()
     def forward(self, h):

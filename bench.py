@@ -186,6 +186,7 @@ class Layer:
       mode "tp-ar" plain all-reduce of the bf16 partials after o and down (activations replicated)."""
 
     def __init__(self, torch, agemm, M, dev, workload="llama3-8b", seed=0, world=1, rank=0, sp=True, fused=True, slabs=1):
+        import numpy as np
         from tests._util import make_acts
         from arcquant_b200 import tp
         self.torch, self.agemm, self.M, self.world, self.rank, self.dev = torch, agemm, M, world, rank, dev
@@ -221,18 +222,21 @@ class Layer:
                 qw, sfw = agemm.reorder_quantize_w((w / sw).to(torch.bfloat16).to(dev), idx_d, KE)
                 ws.append((N, qw, sfw, float(sw)))
             K = KQ + KE
+            # the activations are pre-scaled to +-2688 like the callers' x / scale_x (qLlamaLayer.py:73-77); alpha carries the
+            # scale back: scale_x of a tensor whose largest magnitude was 8.0, so that the outputs have realistic O(1) size
+            sx = float(np.float32(8.0) / np.float32(2688.0))
             it = {"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host, "reduce": row, "gather": gather,
                   "x": x_host.to(dev), "w_sep": ws, "Ns": Ns}
             # launch list: (label, N, qw, sfw, alpha, col_scale, epilogue, out_cols)
             if fused and name == "gate_up" and Ns[0] % 128 == 0:
                 qw, sfw, cs = agemm.interleave_gate_up(tuple(ws[0][1:]), tuple(ws[1][1:]))
-                it["launches"] = [("gate_up+swiglu", 2 * Ns[0], qw, sfw, 1.0, cs, agemm.EPILOGUE_SWIGLU, Ns[0])]
+                it["launches"] = [("gate_up+swiglu", 2 * Ns[0], qw, sfw, sx, cs, agemm.EPILOGUE_SWIGLU, Ns[0])]
             elif fused and len(ws) > 1 and all(n % 128 == 0 for n in Ns):
                 qw, sfw, cs = agemm.fuse_weights([w[1:] for w in ws])
-                it["launches"] = [("+".join(["q", "k", "v"][:len(ws)]), sum(Ns), qw, sfw, 1.0, cs, agemm.EPILOGUE_NONE, sum(Ns))]
+                it["launches"] = [("+".join(["q", "k", "v"][:len(ws)]), sum(Ns), qw, sfw, sx, cs, agemm.EPILOGUE_NONE, sum(Ns))]
             else:
-                it["launches"] = [(name if len(ws) == 1 else "%s[%d]" % (name, j), N, qw, sfw, sw, None, agemm.EPILOGUE_NONE, N)
-                                  for j, (N, qw, sfw, sw) in enumerate(ws)]
+                it["launches"] = [(name if len(ws) == 1 else "%s[%d]" % (name, j), N, qw, sfw, float(np.float32(sx) * np.float32(sw)), None,
+                                   agemm.EPILOGUE_NONE, N) for j, (N, qw, sfw, sw) in enumerate(ws)]
             it["y"] = [torch.empty((M, l[7]), dtype=torch.bfloat16, device=dev) for l in it["launches"]]
             it["y_host"] = [torch.empty((My, l[7]), dtype=torch.bfloat16).pin_memory() for l in it["launches"]]
             if gather:

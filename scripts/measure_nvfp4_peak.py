@@ -90,8 +90,25 @@ def scaled_mm_callable(qa, sfa, qb, sfb, M, N, K):
     return None, " | ".join(errs)
 
 
+def load_refgemm():
+    """oracle/_ref/libarcq_refgemm.so: the reference's CUTLASS GEMM retargeted Sm120 -> Sm100 (oracle/ref_cutlass_gemm.cu)."""
+    so = os.path.join(ROOT, "oracle", "_ref", "libarcq_refgemm.so")
+    if not os.path.exists(so):
+        return None
+    L = ctypes.CDLL(so)
+    vp, i = ctypes.c_void_p, ctypes.c_int
+    L.arcq_refgemm.argtypes = [i, vp, vp, vp, vp, i, i, i, ctypes.c_float, vp, vp, ctypes.c_longlong, vp]
+    L.arcq_refgemm.restype = i
+    return L
+
+
+REFGEMM_VARIANTS = {0: "256x256x256 cluster 2x4 (CUTLASS example 72a)", 1: "256x256x256 cluster 2x1", 2: "128x128x256 cluster 1x1 (nvfp4.cu:32-33 tile)"}
+
+
 def gemm_section():
     out = []
+    RG = load_refgemm()
+    ws = torch.empty(64 << 20, dtype=torch.uint8, device=dev)
     shapes = [(8192, 8192, 8192), (8192, 14336, 4352), (8192, 4096, 14848), (8192, 4096, 4352), (8192, 1024, 4352), (8192, 6144, 4352),
               (8192, 28672, 4352)]
     for M, N, K in shapes:
@@ -116,6 +133,21 @@ def gemm_section():
             got = y.float()
             rec["ours_vs_cublaslt_rel_fro"] = float((got - ref).norm() / ref.norm())
             rec["ours_over_cublaslt_burst"] = rec["ours_tflops_burst"] / rec["cublaslt_tflops_burst"]
+        if RG is not None:
+            st = torch.cuda.current_stream().cuda_stream
+            for v, what in REFGEMM_VARIANTS.items():
+                yr = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
+                call = lambda: RG.arcq_refgemm(v, qa.data_ptr(), qb.data_ptr(), sfa.data_ptr(), sfb.data_ptr(), M, N, K, 1e-3, yr.data_ptr(),  # noqa: E731
+                                               ws.data_ptr(), ws.numel(), st)
+                rc = call()
+                torch.cuda.synchronize()
+                if rc != 0:
+                    rec["ref_cutlass_v%d" % v] = {"config": what, "error": rc}
+                    continue
+                best, med = time_fn(call)
+                rec["ref_cutlass_v%d" % v] = {"config": what, "us_best": best, "tflops_burst": flops / best / 1e6,
+                                              "ours_vs_ref_rel_fro": float((y.float() - yr.float()).norm() / yr.float().norm()),
+                                              "ours_speedup": best / rec["ours_us_best"]}
         out.append(rec)
         del qa, sfa, qb, sfb, y
     return out

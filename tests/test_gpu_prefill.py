@@ -100,3 +100,25 @@ def test_fused_launches_equal_the_reference_launch_structure():
     assert n1 - n0 == cfg.layers * (4 + 2 + 4) and n2 - n1 == cfg.layers * (4 + 7)   # fused: + 2 absmax pre-passes
     diff = float((yf.float() - yu.float()).abs().max())
     assert torch.equal(yf, yu) or diff <= 2 ** -6 * float(yu.float().abs().max()), diff
+
+
+def test_prefill_runs_on_calibration_artifacts(tmp_path):
+    """The on-disk schema of the reference's calibration (./saved/*_{reorder_index,select_num}_*.pt) drives the layers."""
+    from arcquant_b200 import calib as C
+    cfg = prefill.PrefillConfig.named("tiny")
+    ri, sn, sc = C.synthetic_artifacts(cfg.hidden, cfg.intermediate, cfg.layers, seed=1)
+    C.save_artifacts("tiny", ri, sn, sc, root=str(tmp_path))
+    ri, sn, _ = C.load_artifacts("tiny", root=str(tmp_path))
+    dev = torch.device("cuda:0")
+    model = prefill.ArcPrefillModel(cfg, dev, seed=3, keep_ref=True, calib=(ri, sn))
+    assert model.layers[1].down.select_num == sn[C.key(1, "mlp", "down_proj")]
+    assert torch.equal(model.layers[0].idx_h1.cpu(), ri[C.key(0, "self_attn", "q_proj")].to(torch.int16))
+    g = torch.Generator(device=dev).manual_seed(0)
+    h = torch.randn(2, 128, cfg.hidden, device=dev, generator=g).to(torch.bfloat16)
+    y = model(h)
+    ref = h
+    for layer in model.layers:
+        ref = prefill.reference_layer_forward(layer, ref)
+    torch.cuda.synchronize()
+    d, r = (y.float() - h.float()), (ref - h.float())
+    assert float((d - r).norm() / r.norm()) < 0.35

@@ -102,3 +102,39 @@ def test_plan_build_rejects_a_non_permutation():
     idx[5] = 6
     L, rc, _ = _plan(np.ascontiguousarray(idx))
     assert rc != 0 and b"permutation" in L.arcq_last_error()
+
+
+# ---- calibration artefacts in the reference's on-disk schema (arcquant_b200/calib.py) --------------------------------
+
+def test_calibration_artifacts_roundtrip_in_the_reference_schema(tmp_path):
+    from arcquant_b200 import calib as C
+    ri, sn, sc = C.synthetic_artifacts(hidden=512, intermediate=1536, n_layers=2, seed=3)
+    # the reference's own lookups: model/qLlamaLayer.py:237-261, benchmarks/modeling_arc.py:95-106, model_utils.py:38-42
+    nameTemplate = 'layers.{}.{}.{}.{}'
+    for i in range(2):
+        for block, projs in (("self_attn", C.ATTN_PROJS), ("mlp", C.MLP_PROJS)):
+            for proj in projs:
+                k = nameTemplate.format(i, block, proj, 'input')
+                assert k in ri and k in sn and sn[k] % 64 == 0 and ri[k].dtype == torch.int64
+        assert torch.equal(ri[C.key(i, "self_attn", "q_proj")], ri[C.key(i, "self_attn", "k_proj")])   # shared input
+        assert ri[C.key(i, "mlp", "down_proj")].numel() == 1536
+    C.validate(ri, sn)
+    # outliers last (utilize.py:42): the last select_num reordered channels carry the largest statistics
+    k = C.key(0, "mlp", "down_proj")
+    assert sc[k][ri[k][-sn[k]:]].min() >= sc[k][ri[k][:-sn[k]]].max()
+    paths = C.save_artifacts("Llama-Tiny", ri, sn, sc, root=str(tmp_path))
+    assert paths["reorder_index"].endswith("llama-tiny_reorder_index_wikitext2_max.pt")   # reorder_indices.py:88
+    ri2, sn2, sc2 = C.load_artifacts("llama-tiny", root=str(tmp_path))
+    assert sn2 == sn and all(torch.equal(ri2[k], ri[k]) for k in ri) and all(torch.equal(sc2[k], sc[k]) for k in sc)
+    e = C.layer_entries(ri2, sn2, 1)
+    assert e["qkv"][0].dtype == torch.int16 and e["down"][1] == sn[C.key(1, "mlp", "down_proj")]
+    with pytest.raises(FileNotFoundError):
+        C.load_artifacts("absent-model", root=str(tmp_path))
+    bad = dict(ri)
+    bad[k] = ri[k].clone()
+    bad[k][0] = bad[k][1]
+    with pytest.raises(ValueError):
+        C.validate(bad, sn)
+    with pytest.raises(ValueError):
+        C.validate(ri, {**sn, k: 100})
+    assert C.select_num_for(4096, 0.06) == 256 and C.select_num_for(4096, 0.0) == 0
