@@ -5,8 +5,9 @@ A "step" is one pass of the hot path over one batch of M synthetic tokens throug
 layer (Llama-3-8B by default; --workload llama3-70b = BASELINE.json config 4), i.e. what the reference's layers ask of
 `agemm` per layer (model/qLlamaLayer.py:296-303,364-367,429-443):
 
-  default      4 quantise + 4 GEMM launches: q/k/v run as ONE launch over the concatenated weight (per-column scales) and
-               gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (SURVEY.md §8 f2/f3);
+  default      4 quantise + 5 GEMM launches: q/k/v run as ONE launch over the concatenated weight with per-column scales
+               (SURVEY.md §8 f3); gate and up stay two launches;
+  --swiglu     gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (§8 f2; 4 + 4 launches);
   --unfused    the reference's launch structure, 4 quantise + 7 GEMM launches (A/B).
 
 `value` = useful GEMM FLOPs (2*M*N*(KQ+KE), ARC columns included; identical for both structures) of the step / device
@@ -185,7 +186,7 @@ class Layer:
                    cut into slabs and the collective of slab i runs on a communication stream under the GEMM of slab i+1;
       mode "tp-ar" plain all-reduce of the bf16 partials after o and down (activations replicated)."""
 
-    def __init__(self, torch, agemm, M, dev, workload="llama3-8b", seed=0, world=1, rank=0, sp=True, fused=True, slabs=1):
+    def __init__(self, torch, agemm, M, dev, workload="llama3-8b", seed=0, world=1, rank=0, sp=True, fused=True, slabs=1, swiglu=False):
         import numpy as np
         from tests._util import make_acts
         from arcquant_b200 import tp
@@ -228,10 +229,10 @@ class Layer:
             it = {"name": name, "KQ": KQ, "KE": KE, "idx": idx_d, "x_host": x_host, "reduce": row, "gather": gather,
                   "x": x_host.to(dev), "w_sep": ws, "Ns": Ns}
             # launch list: (label, N, qw, sfw, alpha, col_scale, epilogue, out_cols)
-            if fused and name == "gate_up" and Ns[0] % 128 == 0:
+            if swiglu and name == "gate_up" and Ns[0] % 128 == 0:
                 qw, sfw, cs = agemm.interleave_gate_up(tuple(ws[0][1:]), tuple(ws[1][1:]))
                 it["launches"] = [("gate_up+swiglu", 2 * Ns[0], qw, sfw, sx, cs, agemm.EPILOGUE_SWIGLU, Ns[0])]
-            elif fused and len(ws) > 1 and all(n % 128 == 0 for n in Ns):
+            elif fused and name == "qkv" and all(n % 128 == 0 for n in Ns):
                 qw, sfw, cs = agemm.fuse_weights([w[1:] for w in ws])
                 it["launches"] = [("+".join(["q", "k", "v"][:len(ws)]), sum(Ns), qw, sfw, sx, cs, agemm.EPILOGUE_NONE, sum(Ns))]
             else:
@@ -292,31 +293,39 @@ class Layer:
         return outs
 
     def _item_slabs(self, it, x):
-        """Tokens cut into slabs: the collective of slab s runs on the communication stream while the kernels of slab
-        s + 1 run on the compute stream (chunk the row-parallel GEMM along M, reduce chunk i under chunk i+1)."""
+        """Tokens cut into S slabs (micro-batches) that flow through the layer independently: slab s of a linear depends only
+        on slab s of the linear before it.  Collectives run on a communication stream; the compute stream meanwhile works on
+        the other slabs, across linears (reduce chunk i under the GEMM of chunk i+1).  self.dep[s] = event
+        after the last collective that produced slab s (the next linear's slab s waits for it, nothing else does)."""
         ag, torch, dist = self.agemm, self.torch, self.dist
         cur, comm, S, W = torch.cuda.current_stream(), self.comm, self.slabs, self.world
         K = it["KQ"] + it["KE"]
+        capturing = torch.cuda.is_current_stream_capturing()
         if it["reduce"]:
             ms = self.M // S                      # rows of a slab; each rank keeps ms / W of them
-            qx, sfx = ag.reorder_quantize_x(x, it["idx"], it["KE"])
-            it["last_q"] = (qx, sfx)
+            qs = []
             for s in range(S):
-                sf_lo = s * ms * K // 16          # whole 128-row scale blocks: a slab's scales are one contiguous run
-                outs = self._gemms(it, qx[s * ms:(s + 1) * ms], sfx[sf_lo:], (s * ms, (s + 1) * ms))
+                if self.dep[s] is not None:
+                    cur.wait_event(self.dep[s])
+                qs.append(ag.reorder_quantize_x(x[s * ms:(s + 1) * ms], it["idx"], it["KE"]))
+            it["last_q"] = qs
+            for s in range(S):
+                outs = self._gemms(it, qs[s][0], qs[s][1], (s * ms, (s + 1) * ms))
                 ev = torch.cuda.Event(); ev.record(cur)
                 with torch.cuda.stream(comm):
                     comm.wait_event(ev)
                     for j, y in enumerate(outs):
-                        # rank r keeps rows [s*ms/W*... ] of slab s: y_rs is laid out [slab][ms / W rows]
+                        # rank r keeps rows [r ms / W, (r + 1) ms / W) of slab s: y_rs is laid out [slab][ms / W rows]
                         dist.reduce_scatter_tensor(it["y_rs"][j][s * ms // W:(s + 1) * ms // W], y)
-            cur.wait_stream(comm)
+                    self.dep[s] = torch.cuda.Event(); self.dep[s].record(comm)
             return it["y_rs"]
         # column-parallel: quantise slab s of the rank's own tokens, gather it on the communication stream, GEMM when it lands
         mx = x.shape[0] // S                      # own rows per slab
         mg = mx * W                               # gathered rows per slab
         evs = []
         for s in range(S):
+            if self.dep[s] is not None:
+                cur.wait_event(self.dep[s])
             qx, sfx = ag.reorder_quantize_x(x[s * mx:(s + 1) * mx], it["idx"], it["KE"])
             ev = torch.cuda.Event(); ev.record(cur)
             with torch.cuda.stream(comm):
@@ -324,18 +333,22 @@ class Layer:
                 dist.all_gather_into_tensor(it["qx_full"][s * mg:(s + 1) * mg], qx)
                 dist.all_gather_into_tensor(it["sfx_full"][s * mg * K // 16:(s + 1) * mg * K // 16], sfx[:mx * K // 16])
                 e2 = torch.cuda.Event(); e2.record(comm)
-            if not torch.cuda.is_current_stream_capturing():
+            if not capturing:
                 qx.record_stream(comm); sfx.record_stream(comm)
             evs.append(e2)
         it["last_q"] = (it["qx_full"], it["sfx_full"])
         for s in range(S):
             cur.wait_event(evs[s])
             self._gemms(it, it["qx_full"][s * mg:(s + 1) * mg], it["sfx_full"][s * mg * K // 16:], (s * mg, (s + 1) * mg))
+            self.dep[s] = None                    # the next linear's slab s follows on the compute stream itself
         return it["y"]
 
     def step(self, events=None):
+        self.dep = [None] * max(1, self.slabs)
         for it in self.items:
             it["outs"] = self._item(it, it["x"], events)
+        if self.slabs > 1:
+            self.torch.cuda.current_stream().wait_stream(self.comm)
 
     def step_e2e(self):
         """Same step through the public API with HOST buffers: H2D of every activation (pinned -> device) and D2H of
@@ -355,10 +368,13 @@ class Layer:
                 self._h2d.wait_event(it["ev_read"])  # the previous step's quantise has consumed x_in
                 it["x_in"].copy_(it["x_host"], non_blocking=True)
                 it["ev_in"].record(self._h2d)
+        self.dep = [None] * max(1, self.slabs)
         for it in self.items:
             cur.wait_event(it["ev_in"])
             cur.wait_event(it["ev_out"])  # the previous step's D2H of this item's result buffers is done
             outs = self._item(it, it["x_in"])
+            if self.slabs > 1:
+                cur.wait_stream(self.comm)  # the reduce-scattered result is produced on the communication stream
             it["ev_read"].record(cur)
             it["ev_y"].record(cur)
             with torch.cuda.stream(self._d2h):
@@ -405,7 +421,12 @@ class Layer:
         torch.cuda.synchronize()
         for it in self.items:
             K = it["KQ"] + it["KE"]
-            qx, sfx = it["last_q"]
+            if isinstance(it["last_q"], list):   # row-parallel linear quantised slab by slab: the slabs are contiguous row ranges
+                qx = torch.cat([q for q, _ in it["last_q"]])
+                nsl = qx.shape[0] // len(it["last_q"]) * K // 16
+                sfx = torch.cat([sf[:nsl] for _, sf in it["last_q"]] + [torch.zeros(128 * K // 16, dtype=torch.uint8, device=self.dev)])
+            else:
+                qx, sfx = it["last_q"]
             # (1) this rank's own quantise output: rebuild it from x and compare sampled rows with the CPU oracle
             q_own, sf_own = self.agemm.reorder_quantize_x(it["x"], it["idx"], it["KE"])
             rows = T.sample_rows(it["x"].shape[0], per_block=1, seed=it["KQ"])[:48]
@@ -505,7 +526,7 @@ def run_native(args):
     tp_mode = world > 1 and args.parallelism in ("tp", "tp-ar")
     slabs = args.slabs if (tp_mode and args.parallelism == "tp") else 1
     layer = Layer(torch, agemm, M, dev, workload=args.workload, world=world if tp_mode else 1, rank=rank if tp_mode else 0,
-                  sp=args.parallelism == "tp", fused=not args.unfused, slabs=slabs)
+                  sp=args.parallelism == "tp", fused=not args.unfused, slabs=slabs, swiglu=args.swiglu)
     layer.dist = dist
 
     def barrier():
@@ -692,7 +713,7 @@ def run_native(args):
         "vs_baseline": None, "dtype": "nvfp4 (e2m1 x e2m1, ue4m3 block scales, fp32 accumulate, bf16 out)",
         "data": "synthetic",
         "config": {"workload": "%s decoder-layer linears (qkv, o, gate/up, down): %s%s" % (
-                       args.workload, structure, "" if args.unfused else " (q/k/v fused, gate/up fused with SwiGLU epilogue)"),
+                       args.workload, structure, "" if args.unfused else (" (q/k/v fused, gate/up fused with SwiGLU epilogue)" if args.swiglu else " (q/k/v fused)")),
                    "tokens_global": M if (tp_mode or world == 1) else M * world,
                    "tokens_per_gpu": (M // world if (tp_mode and layer.sp) else M),
                    "select_num": {n: ke for n, _, ke, _ in layer_items(args.workload)},
@@ -756,6 +777,9 @@ def main():
                          "with plain all-reduce (tp-ar), or independent token replicas")
     ap.add_argument("--slabs", type=int, default=2, help="tp: token slabs whose collectives overlap the next slab's kernels")
     ap.add_argument("--unfused", action="store_true", help="7 GEMM launches per step (the reference's launch structure)")
+    ap.add_argument("--swiglu", action="store_true",
+                    help="gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (what the prefill harness runs: it also "
+                         "replaces torch's SiLU*up pass, which this step does not contain, so here it only shows the epilogue's cost)")
     ap.add_argument("--no-graph", action="store_true", help="tp: launch from Python instead of replaying a CUDA graph")
     ap.add_argument("--no-check", action="store_true", help="skip the oracle check of the last step's outputs")
     ap.add_argument("--no-prefill", action="store_true", help="skip the config-3 prefill line (N=1)")
