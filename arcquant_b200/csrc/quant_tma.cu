@@ -10,7 +10,7 @@ struct Cfg { int R, threads, minb, S, RT; };
 
 // one translation unit per tile organisation (quant_tma_cfg.cu compiled with -DARCQ_CFG_*; see build.py)
 #define ARCQ_CFG_DECL(RR, RTT, TH, MB) \
-  int launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st);
+  int launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st, bool own2);
 ARCQ_CFG_DECL(4, 4, 256, 2) ARCQ_CFG_DECL(4, 4, 512, 1) ARCQ_CFG_DECL(2, 2, 256, 2) ARCQ_CFG_DECL(2, 2, 512, 1) ARCQ_CFG_DECL(1, 1, 512, 1)
 ARCQ_CFG_DECL(8, 8, 512, 1) ARCQ_CFG_DECL(8, 4, 512, 1)
 #undef ARCQ_CFG_DECL
@@ -53,16 +53,19 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
   own = ngroups * (c.R / c.RT) <= c.threads;
   QuantParams pp = p;
   bool planned = want_plan && plan_usable(c.R, p.KQ);
-  if (planned && (carve_t(c.R, p.KQ, p.KE, rms, false, c.S, true).total + 1024) * c.minb > kSmemPerSm) {
-    if (c.S > 1 && (carve_t(c.R, p.KQ, p.KE, rms, false, 1, true).total + 1024) * c.minb <= kSmemPerSm) c.S = 1;  // trade the second staging slot
-    else planned = false;
+  // two owned groups per thread (offsets in registers, no table in shared memory): planned 4- and 2-row tiles whose byte
+  // offsets fit 16 bits
+  bool own2 = planned && !own && c.R == c.RT && c.R <= 4 && ngroups <= 2 * c.threads && p.KQ * 2 * c.R <= 65536;
+  if (planned && (carve_t(c.R, p.KQ, p.KE, rms, false, c.S, true, own2).total + 1024) * c.minb > kSmemPerSm) {
+    if (c.S > 1 && (carve_t(c.R, p.KQ, p.KE, rms, false, 1, true, own2).total + 1024) * c.minb <= kSmemPerSm) c.S = 1;  // trade the second staging slot
+    else planned = own2 = false;
   }
   pp.plan = planned ? p.plan + (int64_t)plan_section(c.R) * p.KQ : nullptr;   // this tile height's section
   tab32 = !own && !planned && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
-  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
+  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned, own2).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
 #define ARCQ_T(RR, RTT, TH, MB) \
   if (c.R == RR && c.RT == RTT && c.threads == TH && c.minb == MB) \
-    return launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(pp, flavour, is_w, rms, c.S, tab32, own, stream);
+    return launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(pp, flavour, is_w, rms, c.S, tab32, own, stream, own2);
   ARCQ_T(4, 4, 256, 2) ARCQ_T(4, 4, 512, 1) ARCQ_T(2, 2, 256, 2) ARCQ_T(2, 2, 512, 1) ARCQ_T(1, 1, 512, 1)
   ARCQ_T(8, 8, 512, 1) ARCQ_T(8, 4, 512, 1)
 #undef ARCQ_T

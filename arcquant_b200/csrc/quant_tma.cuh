@@ -37,7 +37,7 @@ struct CarveT {  // shared-memory layout (bytes), computed identically on host a
 // bytes added to every staged row: the 8 row addresses of one ldmatrix must fall into 8 different 16-byte bank groups.
 // Plan mode reads (two tile rows) x (four 8-channel blocks) per matrix: the odd tile row must sit 64 bytes off.
 __host__ __device__ constexpr int stage_pad_of(int R, bool plan) { return plan ? 64 : stage_pad(R); }
-__host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool tab32, int S, bool plan = false) {
+__host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool tab32, int S, bool plan = false, bool own2 = false) {
   CarveT c;
   int o = 128;                  // mbarriers full[S] (S <= 4)
   c.lut = o; o += 2 * 128 * 4;  // rcp + sf LUTs
@@ -47,7 +47,7 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
 #ifdef ARCQ_STASH_LRMAJOR
   o += R * 16;  // experiment: [row][group] stash, rows padded by 16 bytes (conflict-free STS.128 and LDS.128)
 #endif
-  c.tab = o; o += KQ * (tab32 ? 4 : 2);
+  c.tab = o; if (!own2) o += KQ * (tab32 ? 4 : 2);   // own2: the table only lives during set-up, on top of the (still empty) tile
   o = (o + 15) & ~15;
   c.tabt = o; if (plan) o += KQ * 2;   // planned chunk positions in the order the transposing lanes need them
   o = (o + 15) & ~15;
@@ -57,6 +57,7 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
   c.rstd = o; if (rms) o += 64;
   o = (o + 127) & ~127;
   c.tile = o; o += KQ * 2 * R;
+  if (own2) c.tab = c.tile;
   c.stage = o; o += S * (KQ * 2 + stage_pad_of(R, plan)) * R;
   c.total = o;
   return c;
@@ -64,7 +65,10 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
 
 // PS: fused per-tensor pre-scale (activations only): every gathered element becomes bf16(x / (amax / 2688)) first
 // PLAN: chunk positions come from a conflict-free placement plan (plan.cu) instead of the arithmetic swizzle
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN>
+// OWN2: every thread owns up to TWO 16-groups (KQ/16 <= 2 * THREADS) and keeps their 32 gather offsets packed in 16
+// registers, so the per-tile loads of the offset table (a third of the gather's shared-memory traffic for 2-row tiles)
+// disappear and the table's shared memory goes to a second staging slot
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN, bool OWN2 = false>
 __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantParams p, const int S) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int CB = 2 * R;        // bytes of one channel chunk
@@ -77,7 +81,8 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
   const int KQ = p.KQ, KE = p.KE, K = KQ + KE;
   const int G = (KQ - KE) / 16, ngroups = KQ / 16, nunits = KQ / 8, nchunks = K / 64;
   static_assert(!PLAN || (!RMS && (R == 8 || R == 4 || R == 2)), "plans exist for the matrix-transposed tiles");
-  const CarveT cv = carve_t(R, KQ, KE, RMS, TAB32, S, PLAN);
+  static_assert(!OWN2 || (PLAN && !OWN && !TAB32 && R == RT), "two owned groups per thread: planned, one row block per tile");
+  const CarveT cv = carve_t(R, KQ, KE, RMS, TAB32, S, PLAN, OWN2);
   uint64_t *full = reinterpret_cast<uint64_t *>(smem);
   float *rcp_lut = reinterpret_cast<float *>(smem + cv.lut), *sf_lut = rcp_lut + 128;
   const int sfs_bytes = nchunks * 4 * R;
@@ -225,6 +230,19 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
   uint32_t own_off[OWN ? 16 : 1];
   if constexpr (OWN) load_offsets(tid / RB < ngroups ? tid / RB : 0, own_off);
+  uint32_t own2[OWN2 ? 16 : 1];   // [item][8]: two byte offsets (< 65536) per word
+  if constexpr (OWN2) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int g = tid + it * THREADS < ngroups ? tid + it * THREADS : 0;
+      const uint4 *t4 = reinterpret_cast<const uint4 *>(smem + cv.tab) + 2 * g;
+      const uint4 a = t4[0], b = t4[1];
+      const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int q = 0; q < 8; ++q) own2[it * 8 + q] = w[q] * CB;   // both halves: position * CB < 65536, no carry
+    }
+    __syncthreads();   // the table sat on top of the tile: everybody has its offsets before the first transposition writes there
+  }
   PrescaleCtx psc = {1.0f, 1.0f, false};
   if constexpr (PS) {
     float scale_fp32;
@@ -435,7 +453,12 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     }
 
     // ---- phase A: permuted gather + primary quantisation; one item = (16-group, block of RT rows) per thread per step ----
-    for (int item = tid; item < ngroups * RB; item += THREADS) {
+    constexpr int NIT = OWN2 ? 2 : 1;
+    for (int item0 = tid; item0 < ngroups * RB; item0 += NIT * THREADS) {
+#pragma unroll
+     for (int it = 0; it < NIT; ++it) {
+      const int item = item0 + it * THREADS;
+      if (NIT > 1 && item >= ngroups * RB) break;
       const int g = item / RB, rb = item % RB;
       uint32_t v[16][RTP];
       if (ARCQ_DBG(p, 2)) {
@@ -446,6 +469,9 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       } else if constexpr (OWN) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + own_off[i] + rb * (2 * RT), v[i]);
+      } else if constexpr (OWN2) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) lds_chunk<RT>(tile + ((own2[it * 8 + (i >> 1)] >> (16 * (i & 1))) & 0xffffu), v[i]);
       } else {
         uint32_t off[16];
         load_offsets(g, off);
@@ -532,7 +558,8 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           emit_row(lr, sfb, c_lo, c_hi, sc, xb);
         }
       }
-      if constexpr (OWN) break;  // THREADS >= items: one item per thread, its offsets stay in registers
+     }
+      if constexpr (OWN || OWN2) break;  // every item is owned: its offsets stay in registers
     }
 
     // ---- phase B: ARC residuals, one (group, row) item per thread per step, from the stash of phase A ----
@@ -619,14 +646,14 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
 constexpr int kSmemPerSm = 227 * 1024;
 
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN>
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN, bool OWN2 = false>
 int launch(const QuantParams &p0, int S, cudaStream_t stream) {
   QuantParams p = p0;
 #ifdef ARCQ_EXPERIMENT
   if (const char *e = getenv("ARCQ_QUANT_DEBUG")) p.debug = atoi(e);
 #endif
-  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB, PS, PLAN>;
-  const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S, PLAN).total;
+  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB, PS, PLAN, OWN2>;
+  const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S, PLAN, OWN2).total;
   static SmemAttrCache attr_cache = {};  // per instantiation, per device
   if (int rc = ensure_dynamic_smem(kern, smem, attr_cache)) return rc;
   const int sms = sm_count();
@@ -640,9 +667,12 @@ int launch(const QuantParams &p0, int S, cudaStream_t stream) {
 }
 
 template <int R, int RT, int THREADS, int MINB, int FLAVOUR, bool IS_W, bool RMS, bool PS = false>
-int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t st) {
+int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t st, bool own2 = false) {
   if constexpr (!IS_W && !RMS && (R == 8 || R == 4 || R == 2)) {
     if (p.plan) {  // planned placement: 16-bit position tables only
+      if constexpr (R == RT && R <= 4) {
+        if (own2) return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB, PS, true, true>(p, S, st);
+      }
       if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB, PS, true>(p, S, st);
       return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB, PS, true>(p, S, st);
     }
@@ -653,15 +683,15 @@ int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t s
 }
 
 template <int R, int RT, int THREADS, int MINB>
-int launch_kind(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st) {
+int launch_kind(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32, bool own, cudaStream_t st, bool own2 = false) {
   if (rms) return launch_tab<R, RT, THREADS, MINB, 0, false, true>(p, S, tab32, own, st);
   if (is_w) return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, true, false>(p, S, tab32, own, st)
                                               : launch_tab<R, RT, THREADS, MINB, 0, true, false>(p, S, tab32, own, st);
   if (p.amax)
-    return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false, true>(p, S, tab32, own, st)
-                                      : launch_tab<R, RT, THREADS, MINB, 0, false, false, true>(p, S, tab32, own, st);
-  return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false>(p, S, tab32, own, st)
-                                    : launch_tab<R, RT, THREADS, MINB, 0, false, false>(p, S, tab32, own, st);
+    return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false, true>(p, S, tab32, own, st, own2)
+                                      : launch_tab<R, RT, THREADS, MINB, 0, false, false, true>(p, S, tab32, own, st, own2);
+  return flavour == ARCQ_FLAVOUR_32 ? launch_tab<R, RT, THREADS, MINB, 1, false, false>(p, S, tab32, own, st, own2)
+                                    : launch_tab<R, RT, THREADS, MINB, 0, false, false>(p, S, tab32, own, st, own2);
 }
 
 

@@ -11,8 +11,8 @@
 namespace arcq {
 
 int ARCQ_CFG_CAT(ARCQ_CFG_R, ARCQ_CFG_RT, ARCQ_CFG_TH, ARCQ_CFG_MB)(const QuantParams &p, int flavour, bool is_w, bool rms, int S, bool tab32,
-                                                                   bool own, cudaStream_t st) {
-  return launch_kind<ARCQ_CFG_R, ARCQ_CFG_RT, ARCQ_CFG_TH, ARCQ_CFG_MB>(p, flavour, is_w, rms, S, tab32, own, st);
+                                                                   bool own, cudaStream_t st, bool own2) {
+  return launch_kind<ARCQ_CFG_R, ARCQ_CFG_RT, ARCQ_CFG_TH, ARCQ_CFG_MB>(p, flavour, is_w, rms, S, tab32, own, st, own2);
 }
 
 }  // namespace arcq
