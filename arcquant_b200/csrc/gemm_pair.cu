@@ -38,7 +38,10 @@ constexpr int kBN = 256, kBKBytes = 128, kBK = 256;
 constexpr int kThreadsP = 320;             // warp 0 TMA, warp 1 MMA (leader only issues), warps 2..9 epilogue
 constexpr int kPC = 64;                    // epilogue staging pass width (columns)
 
-template <int STAGES>
+constexpr int kSiluLo = 103, kSiluHi = 133;                       // biased bf16 exponents covered by the silu table: 2^-24 .. 2^7
+constexpr int kSiluEntries = 2 * (kSiluHi - kSiluLo + 1) * 128;   // sign x exponent x 7-bit mantissa = 7936 bf16 values
+
+template <int STAGES, bool LUT = false>
 struct PCfg {
   static constexpr int A_BYTES = kRows * kBKBytes;     // 16 KiB
   static constexpr int B_BYTES = kRows * kBKBytes;     // this CTA's half of the B tile
@@ -48,7 +51,8 @@ struct PCfg {
   static constexpr int SF_COLS = 48, SF_COL0 = kBN, TMEM_COLS = 512;
   static constexpr int EPI_WARP_BYTES = 32 * kPC * 2;
   static constexpr int EPI_BYTES = 8 * EPI_WARP_BYTES;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+  static constexpr int LUT_BYTES = LUT ? kSiluEntries * 2 : 0;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + 1024 + 256 + LUT_BYTES;
   static_assert(SMEM_BYTES <= 232448, "shared memory overflow");
 };
 
@@ -70,15 +74,33 @@ struct PParams {
 // subroutine (measured: 4.6x on the whole GEMM with |x| ~ 100).  Numerator and divisor are therefore brought to mid-range
 // by exact power-of-two factors (x 2^32, / 2^32) and the quotient scaled back by 2^-64: all three steps are exact, the
 // one rounding is the division's, so the result is bit-identical to the plain division.
-__device__ __forceinline__ float swiglu_bf16(float g, float u) {
-  const float gb = __bfloat162float(__float2bfloat16_rn(g)), ub = __bfloat162float(__float2bfloat16_rn(u));
+__device__ __forceinline__ float silu_bf16_exact(float gb) {   // gb holds a bf16 value; returns bf16(silu(gb)) as float
   const float den = 1.0f + expf(-gb);                      // in [1, +inf]
   const bool big = den > 1.0e18f;                          // only for gb < -41: |quotient| < 4e-17, far above denormals
   const float d = fminf(den, 3.4028235e38f) * (big ? 2.3283064365386963e-10f : 1.0f);   // 2^-32
   const float n = gb * (big ? 4294967296.0f : 1.0f);                                     // 2^32
   float q = __fdiv_rn(n, d) * (big ? 5.421010862427522e-20f : 1.0f);                    // 2^-64
   if (den > 3.4028235e38f) q = -0.0f;                      // gb / +inf (gb is negative here)
-  const float s = __bfloat162float(__float2bfloat16_rn(q));
+  return __bfloat162float(__float2bfloat16_rn(q));
+}
+
+// The gate is rounded to bf16 BEFORE silu (torch applies silu to the bf16 GEMM output), so silu is a function of 16 bits.
+// Outside 2^-24 <= |g| < 2^7 it is trivial and exact (g/2 below: 1 + exp(-g) rounds to 2; g above for g > 0: the sum
+// rounds to 1; -0 above for g < 0: exp(-g) overflows), inside it comes from a 7936-entry table that every CTA fills once
+// with silu_bf16_exact -- same bits as the formula, a dozen instructions and one shared load instead of ~45 per output.
+__device__ __forceinline__ uint32_t silu_lut_index(uint32_t bits) {
+  return ((((bits >> 15) & 1u) * (kSiluHi - kSiluLo + 1) + ((bits >> 7) & 0xffu) - kSiluLo) << 7) | (bits & 127u);
+}
+__device__ __forceinline__ float swiglu_bf16(float g, float u, const uint16_t *lut) {
+  const uint32_t gbits = (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(g));
+  const float gb = __uint_as_float(gbits << 16), ub = __bfloat162float(__float2bfloat16_rn(u));
+  const uint32_t e = (gbits >> 7) & 0xffu;
+  const uint32_t idx = min(silu_lut_index(gbits), (uint32_t)(kSiluEntries - 1));   // clamped: the load is unconditional
+  const float t = __uint_as_float((uint32_t)lut[e < kSiluLo ? 0u : idx] << 16);
+  const float small = __bfloat162float(__float2bfloat16_rn(gb * 0.5f));
+  const float large = (gbits & 0x8000u) ? -0.0f : gb;
+  float s = e < kSiluLo ? small : (e > kSiluHi ? large : t);
+  if (e == 255u && gbits != 0x7f80u) s = __uint_as_float(0x7fc00000u);   // NaN in, or -inf / (1 + inf): NaN like the formula
   return __fmul_rn(s, ub);
 }
 
@@ -101,11 +123,19 @@ __global__ void __launch_bounds__(kThreadsP, 1)
 gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                        const __grid_constant__ CUtensorMap tmap_sfa, const __grid_constant__ CUtensorMap tmap_sfb,
                        const PParams p) {
-  using Cfg = PCfg<STAGES>;
+  using Cfg = PCfg<STAGES, SWIGLU>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t *epi = smem + STAGES * Cfg::STAGE_BYTES;
   uint64_t *bars = reinterpret_cast<uint64_t *>(epi + Cfg::EPI_BYTES);
+  uint16_t *silu_lut = reinterpret_cast<uint16_t *>(epi + Cfg::EPI_BYTES + 256);
+  if constexpr (SWIGLU) {   // filled before the first barrier below, read only by the epilogue warps
+    for (int i = threadIdx.x; i < kSiluEntries; i += kThreadsP) {
+      const uint32_t sgn = i / ((kSiluHi - kSiluLo + 1) * 128), rem = i % ((kSiluHi - kSiluLo + 1) * 128);
+      const uint32_t bits = (sgn << 15) | (((rem >> 7) + kSiluLo) << 7) | (rem & 127u);
+      silu_lut[i] = (uint16_t)(__float_as_uint(silu_bf16_exact(__uint_as_float(bits << 16))) >> 16);
+    }
+  }
   uint64_t *full = bars, *empty = bars + STAGES, *tfull = bars + 2 * STAGES, *tempty = tfull + 1;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 1);
 
@@ -290,8 +320,8 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
                 su0 = __shfl_sync(0xffffffffu, sreg[HC / 64 + (col >> 5)], col & 31);
                 su1 = __shfl_sync(0xffffffffu, sreg[HC / 64 + (col >> 5)], (col & 31) + 1);
               }
-              v0 = swiglu_bf16(sg0 * __uint_as_float(r[col >> 5][col & 31]), su0 * __uint_as_float(r[2 + (col >> 5)][col & 31]));
-              v1 = swiglu_bf16(sg1 * __uint_as_float(r[col >> 5][(col & 31) + 1]), su1 * __uint_as_float(r[2 + (col >> 5)][(col & 31) + 1]));
+              v0 = swiglu_bf16(sg0 * __uint_as_float(r[col >> 5][col & 31]), su0 * __uint_as_float(r[2 + (col >> 5)][col & 31]), silu_lut);
+              v1 = swiglu_bf16(sg1 * __uint_as_float(r[col >> 5][(col & 31) + 1]), su1 * __uint_as_float(r[2 + (col >> 5)][(col & 31) + 1]), silu_lut);
             } else {
               float s0 = alpha, s1 = alpha;
               if (cs) {
@@ -343,8 +373,8 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 template <bool SWIGLU>
 static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
                               const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, cudaStream_t stream) {
-  constexpr int STAGES = 5;
-  using Cfg = PCfg<STAGES>;
+  constexpr int STAGES = SWIGLU ? 4 : 5;   // the silu table takes the fifth stage's place
+  using Cfg = PCfg<STAGES, SWIGLU>;
   auto kern = gemm_nvfp4_pair_kernel<STAGES, SWIGLU>;
   static SmemAttrCache attr_cache = {};
   static int max_pairs[kMaxDevices] = {0};   // co-resident CTA pairs, per device

@@ -545,23 +545,31 @@ def run_native(args):
     # step (kernels + NCCL collectives, both streams) in a CUDA graph and replay it
     graph = None
     if tp_mode and not args.no_graph:
+        ok = 1
         try:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 layer.step()
+                torch.cuda.synchronize()
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=side):
+                # thread_local: NCCL's watchdog thread polls events while we capture; that must not invalidate the capture
+                with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
                     layer.step()
             torch.cuda.current_stream().wait_stream(side)
+        except Exception as e:  # noqa: BLE001
+            sys.stderr.write("bench.py[rank %d]: CUDA-graph capture of the tensor-parallel step failed (%s)\n" % (rank, str(e).splitlines()[0][:200]))
+            ok, graph = 0, None
+        # every rank must take the same path: one eager rank against replaying ranks would deadlock in the first collective
+        torch.cuda.synchronize()
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            graph = None
+        else:
             for _ in range(3):
                 graph.replay()
-            barrier()
-        except Exception as e:  # noqa: BLE001
-            if rank == 0:
-                sys.stderr.write("bench.py: CUDA-graph capture of the tensor-parallel step failed (%s); timing plain launches\n" % (e,))
-            graph = None
-            barrier()
+        barrier()
 
     def run_step():
         if graph is not None:

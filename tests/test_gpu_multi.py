@@ -45,9 +45,17 @@ def test_two_rank_step_parity(args):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
            "--master-port", str(_free_port()), os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "3", "--warmup", "1",
            "--tokens", "2048", "--e2e-steps", "1", "--no-cpu-baseline", "--no-prefill"] + args
-    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stderr[-2000:]
-    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    # own process group + hard kill on timeout: a hung rank must not keep the GPUs (and the box) busy
+    p = subprocess.Popen(cmd, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, start_new_session=True)
+    try:
+        out, err = p.communicate(timeout=240)
+    except subprocess.TimeoutExpired:
+        import signal
+        os.killpg(p.pid, signal.SIGKILL)
+        out, err = p.communicate()
+        pytest.fail("2-rank bench timed out: " + err[-1500:])
+    assert p.returncode == 0, err[-2000:]
+    line = [l for l in out.splitlines() if l.startswith("{")][-1]
     out = json.loads(line)
     pc = out["parity_check"]
     assert pc["ranks"] == 2 and pc["ok"], pc
