@@ -544,7 +544,7 @@ def run_native(args):
     # tensor-parallel shards are launch-bound (a few hundred microseconds of kernels against ~20 host calls): capture the
     # step (kernels + NCCL collectives, both streams) in a CUDA graph and replay it
     graph = None
-    if tp_mode and not args.no_graph:
+    if tp_mode and args.graph and not args.no_graph:
         ok = 1
         try:
             side = torch.cuda.Stream()
@@ -634,8 +634,7 @@ def run_native(args):
         parity = layer.check()
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _leave(world)
         return
     per, meta = {}, {}
     for kind, label, KQ, KE, N, rows, out_cols, a, b in events:
@@ -745,8 +744,17 @@ def run_native(args):
         "binding": agemm.BACKEND,
     }
     print(json.dumps(out))
+    _leave(world)
+
+
+def _leave(world):
+    """Multi-rank runs end here without tearing NCCL down: every collective of the run is complete (the ranks have
+    synchronised after the last one), and destroying a communicator that CUDA graphs or a second stream still reference
+    was seen to hang on this pool (torchrun then waits for ever).  Flush and exit the process with status 0."""
+    sys.stdout.flush()
+    sys.stderr.flush()
     if world > 1:
-        dist.destroy_process_group()
+        os._exit(0)
 
 
 def run_prefill(torch, agemm, dev, name="qwen2.5-7b", bsz=4, seq=1024, steps=3):
@@ -783,12 +791,16 @@ def main():
     ap.add_argument("--parallelism", default="tp", choices=["tp", "tp-ar", "replicas"],
                     help="N>1: tensor-parallel shards of one layer with reduce-scatter + quantised all-gather (default), "
                          "with plain all-reduce (tp-ar), or independent token replicas")
-    ap.add_argument("--slabs", type=int, default=2, help="tp: token slabs whose collectives overlap the next slab's kernels")
+    ap.add_argument("--slabs", type=int, default=1,
+                    help="tp: token slabs (micro-batches) whose collectives run on a communication stream under the other slabs' "
+                         "kernels; measured SLOWER than 1 at N=2 (0.97 vs 0.83 ms: split GEMMs + NCCL kernels taking SMs from the "
+                         "persistent GEMM grid), so off by default")
+    ap.add_argument("--graph", action="store_true", help="tp: capture the step (kernels + NCCL) in a CUDA graph and replay it")
     ap.add_argument("--unfused", action="store_true", help="7 GEMM launches per step (the reference's launch structure)")
     ap.add_argument("--swiglu", action="store_true",
                     help="gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (what the prefill harness runs: it also "
                          "replaces torch's SiLU*up pass, which this step does not contain, so here it only shows the epilogue's cost)")
-    ap.add_argument("--no-graph", action="store_true", help="tp: launch from Python instead of replaying a CUDA graph")
+    ap.add_argument("--no-graph", action="store_true", help="(default) tp: launch from Python")
     ap.add_argument("--no-check", action="store_true", help="skip the oracle check of the last step's outputs")
     ap.add_argument("--no-prefill", action="store_true", help="skip the config-3 prefill line (N=1)")
     ap.add_argument("--e2e-steps", type=int, default=5)

@@ -34,8 +34,8 @@ def _need2():
 
 
 @pytest.mark.parametrize("args", [
-    ["--parallelism", "tp"],                                   # default: 2 slabs, CUDA graph
-    ["--parallelism", "tp", "--slabs", "1", "--no-graph"],     # the round-1 schedule
+    ["--parallelism", "tp"],                                   # default: one slab, launched from Python
+    ["--parallelism", "tp", "--slabs", "2", "--graph"],        # micro-batch slabs on a communication stream, CUDA-graph replay
     ["--parallelism", "tp", "--slabs", "4", "--unfused"],
     ["--parallelism", "tp-ar"],
     ["--parallelism", "tp", "--workload", "llama3-70b"],
