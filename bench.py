@@ -5,9 +5,9 @@ A "step" is one pass of the hot path over one batch of M synthetic tokens throug
 layer (Llama-3-8B by default; --workload llama3-70b = BASELINE.json config 4), i.e. what the reference's layers ask of
 `agemm` per layer (model/qLlamaLayer.py:296-303,364-367,429-443):
 
-  default      4 quantise + 5 GEMM launches: q/k/v run as ONE launch over the concatenated weight with per-column scales
-               (SURVEY.md §8 f3); gate and up stay two launches;
-  --swiglu     gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (§8 f2; 4 + 4 launches);
+  default      4 quantise + 4 GEMM launches: q/k/v run as ONE launch over the concatenated weight with per-column scales
+               (SURVEY.md §8 f3) and gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (§8 f2);
+  --no-swiglu  gate and up stay two plain launches (4 + 5);
   --unfused    the reference's launch structure, 4 quantise + 7 GEMM launches (A/B).
 
 `value` = useful GEMM FLOPs (2*M*N*(KQ+KE), ARC columns included; identical for both structures) of the step / device
@@ -467,8 +467,10 @@ class Layer:
                 else:
                     got = y[grows].double()
                     tol = 2.0 ** -8 * ref.abs() + 2.0 ** -18 * mag + 1e-30
-                    res["gemm_max_err_over_tol"] = max(res["gemm_max_err_over_tol"], float(((got - ref).abs() / tol).max()))
-                    res["gemm_rel_fro_max"] = max(res["gemm_rel_fro_max"], float((got - ref).norm() / ref.norm().clamp_min(1e-30)))
+                    in_place_sum = it["reduce"] and not self.sp   # tp-ar: y already holds the all-reduced sum, not the partial
+                    if not in_place_sum:
+                        res["gemm_max_err_over_tol"] = max(res["gemm_max_err_over_tol"], float(((got - ref).abs() / tol).max()))
+                        res["gemm_rel_fro_max"] = max(res["gemm_rel_fro_max"], float((got - ref).norm() / ref.norm().clamp_min(1e-30)))
                     if it["reduce"]:
                         # (4) reduced result = sum over ranks of the partials: float64 sum of every rank's reference
                         tot, tol_sum = ref.clone(), tol.clone() + 2.0 ** -8 * ref.abs()
@@ -480,7 +482,9 @@ class Layer:
                                 got_r = it["y_rs"][j][local].double()
                                 e = (got_r - tot[sel]).abs() / (tol_sum[sel] + 2.0 ** -7 * tot[sel].abs())
                                 res["tp_reduce_max_err_over_tol"] = max(res["tp_reduce_max_err_over_tol"], float(e.max()))
-                        # tp-ar reduces in place (y holds the sum already): the partial check above does not apply
+                        else:
+                            e = (got - tot).abs() / (tol_sum + 2.0 ** -7 * tot.abs())
+                            res["tp_reduce_max_err_over_tol"] = max(res["tp_reduce_max_err_over_tol"], float(e.max()))
                 res["gemm_outputs_checked"] += 1
         if W > 1:
             t = torch.tensor([res["gemm_max_err_over_tol"], res["gemm_rel_fro_max"], res["swiglu_rel_err_max"],
@@ -526,7 +530,7 @@ def run_native(args):
     tp_mode = world > 1 and args.parallelism in ("tp", "tp-ar")
     slabs = args.slabs if (tp_mode and args.parallelism == "tp") else 1
     layer = Layer(torch, agemm, M, dev, workload=args.workload, world=world if tp_mode else 1, rank=rank if tp_mode else 0,
-                  sp=args.parallelism == "tp", fused=not args.unfused, slabs=slabs, swiglu=args.swiglu)
+                  sp=args.parallelism == "tp", fused=not args.unfused, slabs=slabs, swiglu=args.swiglu and not args.unfused)
     layer.dist = dist
 
     def barrier():
@@ -711,6 +715,7 @@ def run_native(args):
         except Exception as e:  # noqa: BLE001
             prefill_res = {"error": str(e).splitlines()[0][:200]}
 
+    layer_swiglu = args.swiglu and not args.unfused
     structure = "%d x reorder+NVFP4+ARC quantize + %d x block-scaled GEMM per step" % (
         len(layer.items), sum(len(it["launches"]) for it in layer.items))
     out = {
@@ -720,7 +725,7 @@ def run_native(args):
         "vs_baseline": None, "dtype": "nvfp4 (e2m1 x e2m1, ue4m3 block scales, fp32 accumulate, bf16 out)",
         "data": "synthetic",
         "config": {"workload": "%s decoder-layer linears (qkv, o, gate/up, down): %s%s" % (
-                       args.workload, structure, "" if args.unfused else (" (q/k/v fused, gate/up fused with SwiGLU epilogue)" if args.swiglu else " (q/k/v fused)")),
+                       args.workload, structure, "" if args.unfused else (" (q/k/v fused, gate/up fused with SwiGLU epilogue)" if layer_swiglu else " (q/k/v fused)")),
                    "tokens_global": M if (tp_mode or world == 1) else M * world,
                    "tokens_per_gpu": (M // world if (tp_mode and layer.sp) else M),
                    "select_num": {n: ke for n, _, ke, _ in layer_items(args.workload)},
@@ -797,9 +802,10 @@ def main():
                          "persistent GEMM grid), so off by default")
     ap.add_argument("--graph", action="store_true", help="tp: capture the step (kernels + NCCL) in a CUDA graph and replay it")
     ap.add_argument("--unfused", action="store_true", help="7 GEMM launches per step (the reference's launch structure)")
-    ap.add_argument("--swiglu", action="store_true",
-                    help="gate/up as ONE launch whose epilogue writes bf16(silu(gate)) * up (what the prefill harness runs: it also "
-                         "replaces torch's SiLU*up pass, which this step does not contain, so here it only shows the epilogue's cost)")
+    ap.add_argument("--no-swiglu", dest="swiglu", action="store_false",
+                    help="keep gate and up as two plain launches (default: ONE launch whose epilogue writes bf16(silu(gate)) * up, "
+                         "which also replaces the callers' torch SiLU*up pass and halves the bytes written)")
+    ap.set_defaults(swiglu=True)
     ap.add_argument("--no-graph", action="store_true", help="(default) tp: launch from Python")
     ap.add_argument("--no-check", action="store_true", help="skip the oracle check of the last step's outputs")
     ap.add_argument("--no-prefill", action="store_true", help="skip the config-3 prefill line (N=1)")
