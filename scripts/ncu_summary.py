@@ -1,5 +1,5 @@
 """profiles/ncu_summary.json from an `ncu --set full` report of scripts/step_prof.py (run here, no GPU needed):
-  python scripts/ncu_summary.py gpurun_out/r1_step.ncu-rep [round-tag]
+  python scripts/ncu_summary.py gpurun_out/r1_step.ncu-rep [round-tag] [names,in,capture,order]
 Also writes profiles/<tag>_step_ncu.txt (the per-launch metric table the numbers come from)."""
 import csv
 import io
@@ -26,6 +26,9 @@ def to_bytes(v, unit):
 
 def main():
     rep, tag = sys.argv[1], (sys.argv[2] if len(sys.argv) > 2 else "r1")
+    global ORDER
+    if len(sys.argv) > 3:  # names of the captured launches in capture order (when -s did not land on a round boundary)
+        ORDER = sys.argv[3].split(",")
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     hdr, units, body = rows[0], rows[1], rows[2:]
