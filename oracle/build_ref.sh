@@ -7,7 +7,10 @@
 # kernels/main.py, benchmarks/modeling_arc.py) copied UNMODIFIED into the git-ignored oracle/_ref/py/ so that the -m gpu
 # test tests/test_gpu_ref_callers.py can run them on top of THIS repo's `agemm` on the GPU box, where /root/reference does
 # not exist.  They never enter the repository's history (oracle/_ref/ is in .gitignore).
-#   usage: oracle/build_ref.sh [probe|kernels|py|all]   (default: all; kernels take ~4 min of nvcc)
+# (d) "gemm": oracle/ref_cutlass_gemm.cu = the reference's CUTLASS block-scaled GEMM instantiation (kernels/src/nvfp4.cu:28-74)
+# retargeted Sm120 -> Sm100 with the tile / cluster of CUTLASS example 72a, against the reference's vendored CUTLASS headers
+# -> oracle/_ref/libarcq_refgemm.so: a device-side GEMM oracle and the "reference config retargeted" number to beat (~3 min).
+#   usage: oracle/build_ref.sh [probe|kernels|py|gemm|all]   (default: all; kernels take ~4 min of nvcc)
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF=/root/reference
@@ -28,6 +31,14 @@ if [ "$WHAT" = py ] || [ "$WHAT" = all ]; then
   cp "$REF/model/qLinearLayer.py" "$REF/model/quantize.py" "$REF/kernels/main.py" "$REF/benchmarks/modeling_arc.py" "$OUT/py/"
   echo "build_ref: copied the reference callers into $OUT/py (git-ignored)"
 fi
+if [ "$WHAT" = gemm ] || [ "$WHAT" = all ]; then
+  if [ ! -f "$OUT/libarcq_refgemm.so" ] || [ "$HERE/ref_cutlass_gemm.cu" -nt "$OUT/libarcq_refgemm.so" ]; then
+    $NVCC -std=c++17 -O2 -w --expt-relaxed-constexpr -Xcompiler -fPIC -gencode arch=compute_100a,code=sm_100a \
+      -DCUTLASS_ARCH_MMA_SM100_SUPPORTED=1 -I"$REF/third-party/cutlass/include" -I"$REF/third-party/cutlass/tools/util/include" \
+      -shared -o "$OUT/libarcq_refgemm.so" "$HERE/ref_cutlass_gemm.cu" &
+    GEMM_PID=$!
+  fi
+fi
 if [ "$WHAT" = kernels ] || [ "$WHAT" = all ]; then
   FLAGS="-std=c++17 -O2 -w --expt-relaxed-constexpr -Xcompiler -fPIC -Xcompiler -fpermissive -gencode arch=compute_100a,code=sm_100a $INC"
   pids=()
@@ -41,3 +52,4 @@ if [ "$WHAT" = kernels ] || [ "$WHAT" = all ]; then
   $NVCC -shared -Wno-deprecated-gpu-targets -o "$OUT/libarcq_refkernels.so" "$OUT/reorder.o" "$OUT/down.o" "$OUT/rmsnorm.o" "$OUT/shim.o"
   echo "build_ref: built $OUT/libarcq_refkernels.so"
 fi
+if [ -n "${GEMM_PID:-}" ]; then wait "$GEMM_PID" && echo "build_ref: built $OUT/libarcq_refgemm.so"; fi
