@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--rms", action="store_true")
     ap.add_argument("--identity", action="store_true", help="identity reorder_index: conflict-free gather (upper bound)")
+    ap.add_argument("--tile", default="", help='force a tile organisation: "R,threads,S,RT,CTAs/SM" (arcq_set_option quant_tile)')
     ap.add_argument("--no-plans", action="store_true", help="arithmetic chunk placement instead of the conflict-free plans (A/B)")
     args = ap.parse_args()
     peak = 6540.0
@@ -30,6 +31,7 @@ def main():
         peak = json.load(open(p))["hbm_gbs"]
     dev = torch.device("cuda:0")
     agemm.use_plans(not args.no_plans)
+    agemm.set_option("quant_tile", args.tile)
     for sh in args.shapes:
         M, KQ, KE = [int(v) for v in sh.split(",")]
         g = torch.Generator().manual_seed(KQ)
