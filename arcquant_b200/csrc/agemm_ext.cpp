@@ -237,7 +237,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           torch::Tensor plan = torch::empty({arcq_plan_entries(KQ)}, torch::kInt16);
           fail(arcq_plan_build(host.data_ptr<int16_t>(), KQ, reinterpret_cast<uint16_t *>(plan.data_ptr<int16_t>())), "arcq_plan_build");
           return plan;
-        }, "host plan (int16 CPU tensor, 3 * KQ entries) of a reorder_index", py::arg("reorder_index"));
+        }, "host plan (int16 CPU tensor, 6 * KQ entries) of a reorder_index", py::arg("reorder_index"));
   m.def("plan_max_conflict", [](const torch::Tensor &idx, int R, const torch::Tensor &plan) {
           torch::Tensor host = idx.to(torch::kCPU).contiguous(), hp = plan.to(torch::kCPU).contiguous();
           return arcq_plan_max_conflict(host.data_ptr<int16_t>(), (int)host.numel(), R, reinterpret_cast<const uint16_t *>(hp.data_ptr<int16_t>()));
@@ -247,7 +247,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           need(reorder_index, "reorder_index", torch::kInt16, 1);
           need(plan, "plan", torch::kInt16, 1);
           const int64_t M = X.size(0), KQ = X.size(1), K = KQ + KE;
-          TORCH_CHECK(reorder_index.numel() == KQ && plan.numel() == 3 * KQ && plan.device() == X.device() && reorder_index.device() == X.device(),
+          TORCH_CHECK(reorder_index.numel() == KQ && plan.numel() == 6 * KQ && plan.device() == X.device() && reorder_index.device() == X.device(),
                       "reorder_index / plan do not match X");
           const c10::cuda::CUDAGuard guard(X.device());
           auto opt = torch::dtype(torch::kUInt8).device(X.device());

@@ -111,7 +111,10 @@ static int max_conflict(const int16_t *idx, int KQ, int R, const uint16_t *pos) 
 
 using namespace arcq;
 
-extern "C" int64_t arcq_plan_entries(int KQ) { return KQ > 0 ? 3 * (int64_t)KQ : 0; }
+// per tile height (8, 4, 2) one section of 2 KQ entries: pos[KQ] (position of channel c) followed by tabt[KQ] (the same
+// positions in the order the transposing lanes need them: tabt[(k 32 + T) J + j] = pos[(256/R) k + 32 j + 8 (T % 4) + T / 4],
+// J = 8/R), so that the kernel fetches both with one bulk copy each instead of KQ dependent L2 lookups per CTA
+extern "C" int64_t arcq_plan_entries(int KQ) { return KQ > 0 ? 6 * (int64_t)KQ : 0; }
 
 extern "C" int arcq_plan_build(const int16_t *idx_host, int KQ, uint16_t *plan_host) {
   if (!idx_host || !plan_host || KQ <= 0 || KQ > 32768 || KQ % 16) { set_error("arcq_plan_build: bad argument (KQ=%d)", KQ); return ARCQ_EINVAL; }
@@ -123,7 +126,8 @@ extern "C" int arcq_plan_build(const int16_t *idx_host, int KQ, uint16_t *plan_h
   }
   for (int s = 0; s < 3; ++s) {
     const int R = kPlanR[s], D = 64 / R;
-    uint16_t *pos = plan_host + (int64_t)s * KQ;
+    uint16_t *pos = plan_host + (int64_t)s * 2 * KQ, *tabt = pos + KQ;
+    for (int c = 0; c < KQ; ++c) tabt[c] = (uint16_t)c;
     if (!plan_usable(R, KQ)) {  // identity placement: a bijection, never used by the launcher for this tile height
       for (int c = 0; c < KQ; ++c) pos[c] = (uint16_t)c;
       continue;
@@ -142,6 +146,11 @@ extern "C" int arcq_plan_build(const int16_t *idx_host, int KQ, uint16_t *plan_h
       pos[c] = (uint16_t)(D * rank[col[c]]++ + col[c]);
     }
     if (max_conflict(idx_host, KQ, R, pos) != 1) { set_error("arcq_plan_build: plan for R=%d is not conflict-free", R); return ARCQ_EINVAL; }
+    const int CW = 256 / R, J = CW / 32;
+    for (int u = 0; u < KQ; ++u) {
+      const int j = u % J, T = (u / J) & 31, k = u / (32 * J);
+      tabt[u] = pos[CW * k + 32 * j + 8 * (T & 3) + (T >> 2)];
+    }
   }
   return ARCQ_OK;
 }
@@ -150,7 +159,7 @@ extern "C" int arcq_plan_build(const int16_t *idx_host, int KQ, uint16_t *plan_h
 // default arithmetic placement of a random permutation gives 3 - 6); -1 if R has no usable section.  For tests and tools.
 extern "C" int arcq_plan_max_conflict(const int16_t *idx_host, int KQ, int R, const uint16_t *plan_host) {
   if (!idx_host || !plan_host || !plan_usable(R, KQ)) return -1;
-  const uint16_t *pos = plan_host + (int64_t)plan_section(R) * KQ;
+  const uint16_t *pos = plan_host + (int64_t)plan_section(R) * 2 * KQ;
   std::vector<char> seen(KQ, 0);
   for (int c = 0; c < KQ; ++c) { if (pos[c] >= KQ || seen[pos[c]]) return 1 << 20; seen[pos[c]] = 1; }
   return max_conflict(idx_host, KQ, R, pos);

@@ -401,7 +401,7 @@ extern "C" int arcq_quantize_x_ex(const void *x, int64_t M, int KQ, const int16_
     set_error("arcq_quantize_x_ex: unknown prescale_mode %d", prescale_mode);
     return ARCQ_EINVAL;
   }
-  if (plan_dev && ((uintptr_t)plan_dev & 1)) { set_error("arcq_quantize_x_ex: misaligned plan"); return ARCQ_EINVAL; }
+  if (plan_dev && ((uintptr_t)plan_dev & 15)) { set_error("arcq_quantize_x_ex: the plan must be 16-byte aligned (it is fetched with bulk copies)"); return ARCQ_EINVAL; }
   if (M == 0) return ARCQ_OK;
   QuantParams p{(const uint16_t *)x, idx, nullptr, (uint8_t *)qx, (uint8_t *)sfx, plan_dev, amax_dev, scale_out, prescale_mode, 0.0f,
                 (int)M, KQ, KE, 0, 0};

@@ -60,7 +60,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     if (c.S > 1 && (carve_t(c.R, p.KQ, p.KE, rms, false, 1, true, own2).total + 1024) * c.minb <= kSmemPerSm) c.S = 1;  // trade the second staging slot
     else planned = own2 = false;
   }
-  pp.plan = planned ? p.plan + (int64_t)plan_section(c.R) * p.KQ : nullptr;   // this tile height's section
+  pp.plan = planned ? p.plan + (int64_t)plan_section(c.R) * 2 * p.KQ : nullptr;   // this tile height's section
   tab32 = !own && !planned && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
   if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned, own2).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
 #define ARCQ_T(RR, RTT, TH, MB) \

@@ -128,11 +128,23 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     for (int s = 0; s < S; ++s) ptx::mbar_init(&full[s], 1);
     ptx::fence_barrier_init();
   }
+  uint64_t *plan_bar = full + 8;              // PLAN: completion of the two set-up bulk copies
+  uint16_t *plan_pos_s = reinterpret_cast<uint16_t *>(OWN2 ? tile + 2 * KQ : tile);   // PLAN: pos[] staged on the still-empty tile
+  if constexpr (PLAN) {
+    if (tid == 0) { ptx::mbar_init(plan_bar, 1); ptx::fence_barrier_init(); }
+  }
   if (p.M % 128) {  // a ragged last block leaves rows of some slots unwritten: give them defined (zero) content
     for (int i = tid; i < S * slot_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
     ptx::fence_proxy_async();
   }
   __syncthreads();
+  if constexpr (PLAN) {   // pos[KQ] -> scratch on the tile, tabt[KQ] -> its table: two bulk copies instead of 2 KQ L2 lookups
+    if (tid == 0) {
+      ptx::mbar_arrive_expect_tx(plan_bar, (uint32_t)KQ * 4);
+      ptx::bulk_load(plan_pos_s, p.plan, (uint32_t)KQ * 2, plan_bar);
+      ptx::bulk_load(smem + cv.tabt, p.plan + KQ, (uint32_t)KQ * 2, plan_bar);
+    }
+  }
   if (warp == IW) {
     for (int s = 0; s < S; ++s) {
       const int tl = blockIdx.x + s * gridDim.x;
@@ -147,6 +159,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     sf_lut[tid] = sf;
     rcp_lut[tid] = __frcp_rn(sf);  // == f32(1.0 / (double)sf) for every E4M3 value (reorder.cu:146)
   }
+  if constexpr (PLAN) ptx::mbar_wait(plan_bar, 0);
   for (int u = tid; u < nunits; u += THREADS) {
     const uint4 w4 = __ldg(reinterpret_cast<const uint4 *>(p.idx) + u);
     const uint32_t ww[4] = {w4.x, w4.y, w4.z, w4.w};
@@ -154,8 +167,8 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       if constexpr (PLAN) {
-        pos[2 * i] = __ldg(p.plan + (ww[i] & 0xffffu));
-        pos[2 * i + 1] = __ldg(p.plan + (ww[i] >> 16));
+        pos[2 * i] = plan_pos_s[ww[i] & 0xffffu];
+        pos[2 * i + 1] = plan_pos_s[ww[i] >> 16];
       } else {
         pos[2 * i] = (uint32_t)(MATX ? chan_pos_m<R>((int)(ww[i] & 0xffffu)) : chan_pos<R>((int)(ww[i] & 0xffffu)));
         pos[2 * i + 1] = (uint32_t)(MATX ? chan_pos_m<R>((int)(ww[i] >> 16)) : chan_pos<R>((int)(ww[i] >> 16)));
@@ -178,16 +191,6 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
       }
       reinterpret_cast<uint4 *>(smem + cv.wtab)[u] =
           make_uint4(wv[0] | (wv[1] << 16), wv[2] | (wv[3] << 16), wv[4] | (wv[5] << 16), wv[6] | (wv[7] << 16));
-    }
-  }
-  if constexpr (PLAN) {
-    // tabt[(k * 32 + T) * J + j] = position of the channel lane T holds after the ldmatrix of sub-step (k, j):
-    // (256/R) k + 32 j + 8 (T % 4) + T / 4 -- one aligned 2J-byte load per lane per step
-    constexpr int CWP = 256 / R, JP = CWP / 32;
-    uint16_t *tabt = reinterpret_cast<uint16_t *>(smem + cv.tabt);
-    for (int u = tid; u < KQ; u += THREADS) {
-      const int j = u % JP, T = (u / JP) & 31, k = u / (32 * JP);
-      tabt[u] = __ldg(p.plan + (CWP * k + 32 * j + 8 * (T & 3) + (T >> 2)));
     }
   }
   __syncthreads();

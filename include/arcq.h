@@ -114,7 +114,8 @@ int arcq_quantize_x_scaled(const void *x, int64_t M, int KQ, const int16_t *idx,
  * bank conflicts of the permuted gather (reorder.cu:115-118) for any permutation.  A plan is only ever an optimisation:
  * the kernel requires it to be a bijection (arcq_plan_build guarantees it) but derives its gather offsets from
  * plan[reorder_index[k]] itself, so a plan built for a DIFFERENT index still gives correct bytes.
- *   arcq_plan_entries(KQ)  number of uint16 entries (3 * KQ: sections for 8-, 4- and 2-row tiles);
+ *   arcq_plan_entries(KQ)  number of uint16 entries (6 * KQ: per 8-, 4- and 2-row tile the position of every channel and
+ *                          the same positions in the order the transposing lanes consume them);
  *   arcq_plan_build        host pointers; ARCQ_EINVAL if idx is not a permutation of [0, KQ);
  *   arcq_plan_max_conflict worst bank-slot multiplicity of any wavefront under a plan for tile height R (1 = none). */
 int64_t arcq_plan_entries(int KQ);

@@ -87,13 +87,13 @@ def test_plan_is_a_conflict_free_bijection(KQ, kind):
     L, rc, plan = _plan(idx)
     assert rc == 0, L.arcq_last_error()
     for s, R in enumerate((8, 4, 2)):
-        sec = plan[s * KQ:(s + 1) * KQ]
+        sec = plan[2 * s * KQ:(2 * s + 1) * KQ]
         assert np.array_equal(np.sort(sec), np.arange(KQ)), "section R=%d is not a bijection" % R
         usable = KQ % (16 * 64 // R) == 0
         assert _conflict(L, idx, R, plan) == (1 if usable else -1)
     # what the plan removes: the identity placement of a random permutation is far from conflict-free
     if kind == "random" and KQ % 512 == 0:
-        ident = np.tile(np.arange(KQ, dtype=np.uint16), 3)
+        ident = np.tile(np.arange(KQ, dtype=np.uint16), 6)
         assert _conflict(L, idx, 2, ident) >= 3
 
 
