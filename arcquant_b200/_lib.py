@@ -31,6 +31,8 @@ SIGNATURES = {
     "arcq_plan_build": (_I32, [_VP, _I32, _VP]),
     "arcq_plan_max_conflict": (_I32, [_VP, _I32, _I32, _VP]),
     "arcq_quantize_x_ex": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _VP, _I32, _VP, _VP, _VP, _VP]),
+    "arcq_linear_noalloc_bytes": (_I64, [_I64, _I32, _I32]),
+    "arcq_linear_noalloc": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _VP, _I64, _F32, _VP, _VP, _VP]),
     "arcq_launch_count": (_I64, []),
     "arcq_last_error": (ctypes.c_char_p, []),
     "arcq_version": (ctypes.c_char_p, []),

@@ -128,6 +128,26 @@ int arcq_quantize_x_ex(const void *x, int64_t M, int KQ, const int16_t *idx, int
                        const uint16_t *plan_dev, const float *amax_dev, int prescale_mode, void *qx,
                        void *sfx, float *scale_out, void *stream);
 
+/* One linear (arcq_quantize_x followed by arcq_gemm_nvfp4: y bf16 [M, N] = alpha * Q(x[:, idx]) . (qw.sfw)^T) for callers
+ * that cannot allocate device memory -- code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc.  NO COUNTERPART IN THE REFERENCE.  The quantised activation
+ * (codes + scale factors) that the two kernels hand to each other lives in a file-scope `static __device__` array of
+ * ARCQ_NOALLOC_SCRATCH_BYTES inside the library (csrc/noalloc.cu; every GPU that loads the library holds it until
+ * exit) instead of caller buffers; the call makes no cudaMalloc / cudaFree / allocating library call.
+ *   arcq_linear_noalloc_bytes(M, KQ, KE)  scratch bytes such a call needs (-1 on a bad shape);
+ *   arcq_linear_noalloc                   ARCQ_EINVAL with a message naming both numbers when that exceeds
+ *                                         ARCQ_NOALLOC_SCRATCH_BYTES (16 MiB: M <= 6 846 at KQ+KE = 4 352,
+ *                                         M <= 2 003 at KQ+KE = 14 848).
+ * Results are byte-identical to the two separate calls (same kernels, same dispatch).  ALL calls on one GPU share the
+ * one array: calls that may overlap on the GPU (different streams without an ordering between them) race on it; calls
+ * on one stream, or otherwise ordered, are safe.  The array keeps the last call's contents; nothing in it has to start
+ * at zero (every byte the GEMM's stored rows depend on is rewritten by the quantiser of the same call). */
+#define ARCQ_NOALLOC_SCRATCH_BYTES (16 * 1024 * 1024)
+int64_t arcq_linear_noalloc_bytes(int64_t M, int KQ, int KE);
+int arcq_linear_noalloc(const void *x, int64_t M, int KQ, const int16_t *idx, int KE, int flavour,
+                        const void *qw, const void *sfw, int64_t N, float alpha, const float *alpha_dev,
+                        void *y, void *stream);
+
 /* name = value override of a shape-driven kernel choice ("" = back to the default).  Every choice computes the same
  * result; the parity tests force each tile organisation through this.  Options: "quant_tile" = "R,threads,S,RT,CTAs/SM",
  * "quant_family" = 3 | 1, "gemm_pair" = 0 | 1, "gemm_bn" = 128 | 256, "gemm_splitk" = 0 | 2 | 4 | 8.  The product
