@@ -35,8 +35,12 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     if (q[0] > 0) c = Cfg{q[0], q[1], q[4], q[2], q[3]};
   }
   const bool want_plan = p.plan != nullptr && !rms && !is_w;
+  // with a plan the gather is conflict-free at any chunk width, which was the 8-row tile's advantage: for KQ <= 4096 the
+  // 4-row tile at two CTAs per SM with ONE staging slot is then 3-4 % faster (profiles/r2_quant_tile_ab.log)
+  const bool prefer4 = want_plan && ngroups <= 256 && plan_usable(4, p.KQ);
   if (c.R == 0) {
     for (const Cfg &k : cands) {
+      if (prefer4 && (k.R == 8 || (k.R == 4 && k.threads == 256 && k.S == 2))) continue;
       if (rms && k.threads < 32 * k.R) continue;
       if (k.R == 8 && ngroups * (k.R / k.RT) > k.threads) continue;  // only with one owned item per thread
       if (k.R == 4 && k.threads == 256 && ngroups > 256) continue;   // two passes per tile: the wide CTA owns its items
