@@ -33,6 +33,16 @@ SIGNATURES = {
     "arcq_quantize_x_ex": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _VP, _I32, _VP, _VP, _VP, _VP]),
     "arcq_linear_noalloc_bytes": (_I64, [_I64, _I32, _I32]),
     "arcq_linear_noalloc": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _VP, _I64, _F32, _VP, _VP, _VP]),
+    "arcq_peer_alloc": (_I32, [_I64, _VP]),
+    "arcq_peer_free": (_I32, [_VP]),
+    "arcq_peer_export": (_I32, [_VP, _VP]),
+    "arcq_peer_open": (_I32, [_VP, _VP]),
+    "arcq_peer_close": (_I32, [_VP]),
+    "arcq_peer_enable": (_I32, [_I32]),
+    "arcq_peer_status": (_I32, [_VP, _VP]),
+    "arcq_gemm_nvfp4_scatter": (_I32, [_VP, _VP, _VP, _VP, _I64, _I64, _I64, _F32, _VP, _VP, _VP, _I32, _I32, _I64, _I64, _VP]),
+    "arcq_peer_reduce": (_I32, [_VP, _VP, _I32, _I32, _I32, _I64, _I64, _I64, _VP, _I64, _VP]),
+    "arcq_peer_allgather": (_I32, [_VP, _I64, _VP, _I64, _VP, _I64, _VP, _I64, _VP, _I32, _I32, _I32, _VP]),
     "arcq_launch_count": (_I64, []),
     "arcq_last_error": (ctypes.c_char_p, []),
     "arcq_version": (ctypes.c_char_p, []),

@@ -20,7 +20,7 @@ EXT_NAME = "_agemm_ext"
 # (tile rows R, rows per item RT, threads, CTAs per SM) of the TMA-staged quantise kernel: one object file each
 QUANT_CFGS = [(4, 4, 256, 2), (4, 4, 512, 1), (2, 2, 256, 2), (2, 2, 512, 1), (1, 1, 512, 1), (8, 8, 512, 1), (8, 4, 512, 1)]
 # source file, or (source file, extra nvcc flags, object name)
-SOURCES = ["runtime.cu", "plan.cu", "quant.cu", "quant_tma.cu", "gemm.cu", "gemm_pair.cu", "gemm_splitk.cu", "noalloc.cu"] + [
+SOURCES = ["runtime.cu", "plan.cu", "quant.cu", "quant_tma.cu", "gemm.cu", "gemm_pair.cu", "gemm_splitk.cu", "noalloc.cu", "peer.cu"] + [
     ("quant_tma_cfg.cu", ["-DARCQ_CFG_R=%d" % r, "-DARCQ_CFG_RT=%d" % rt, "-DARCQ_CFG_TH=%d" % th, "-DARCQ_CFG_MB=%d" % mb],
      "quant_tma_cfg_%d_%d_%d_%d.o" % (r, rt, th, mb)) for r, rt, th, mb in QUANT_CFGS]
 NVCC_FLAGS = [

@@ -65,6 +65,10 @@ struct PParams {
   int64_t ldd;              // row stride of d in elements
   int ptiles_m, ptiles_n;   // 256 x 256 pair tiles
   long long *prof;          // -DARCQ_GEMM_PROFILE builds: per-role cycle counters of block 0/1 (nullable)
+  // reduce-scatter epilogue (peer.cu): rs_rows != 0 -> the 128-row block starting at global row g goes to the
+  // receive buffer of its owner o = g / rs_rows, slot rs_rank: peer_d[o] + ((rs_rank * rs_rows) + g - o * rs_rows) * ldd
+  __nv_bfloat16 *peer_d[ARCQ_MAX_PEERS];
+  int rs_rows, rs_rank;
 };
 
 // bf16(silu(g)) * u exactly as torch computes `F.silu(g) * u` on bf16 tensors: silu in fp32 (x / (1 + exp(-x)), IEEE
@@ -122,7 +126,7 @@ template <int STAGES, bool SWIGLU>
 __global__ void __launch_bounds__(kThreadsP, 1)
 gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                        const __grid_constant__ CUtensorMap tmap_sfa, const __grid_constant__ CUtensorMap tmap_sfb,
-                       const PParams p) {
+                       const __grid_constant__ PParams p) {
   using Cfg = PCfg<STAGES, SWIGLU>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -303,6 +307,11 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       if (lane == 0) ptx::mbar_arrive_cluster(tempty_leader);
       PROF(eld += clock64() - e1;)
       const int row_base = (pm * 2 + (int)rank) * kRows + q * 32;
+      __nv_bfloat16 *dbase = p.d;
+      if (p.rs_rows) {   // this CTA's 128 rows belong to one owner (rs_rows is a multiple of 128): store into its slot over NVLink
+        const int owner = min((pm * 2 + (int)rank) * kRows / p.rs_rows, ARCQ_MAX_PEERS - 1);
+        dbase = p.peer_d[owner] + (int64_t)(p.rs_rank - owner) * p.rs_rows * p.ldd;
+      }
 #pragma unroll
       for (int pass = 0; pass < OUTC / kPC; ++pass) {
 #pragma unroll
@@ -345,7 +354,7 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
           const int grow = row_base + rr;
           if (grow < p.M && gcol < ncols_out) {
-            __nv_bfloat16 *dst = p.d + (size_t)grow * p.ldd + gcol;
+            __nv_bfloat16 *dst = dbase + (int64_t)grow * p.ldd + gcol;
             if (vec_ok && gcol + 8 <= ncols_out) {
               *reinterpret_cast<uint4 *>(dst) = v;
             } else {
@@ -370,9 +379,12 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 
 }  // namespace
 
+struct ScatterArgs { void *const *peer_recv; int world, rank, rows_per_rank; };
+
 template <bool SWIGLU>
 static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                              const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, cudaStream_t stream) {
+                              const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, cudaStream_t stream,
+                              const ScatterArgs *sc = nullptr) {
   constexpr int STAGES = SWIGLU ? 4 : 5;   // the silu table takes the fifth stage's place
   using Cfg = PCfg<STAGES, SWIGLU>;
   auto kern = gemm_nvfp4_pair_kernel<STAGES, SWIGLU>;
@@ -401,7 +413,12 @@ static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, con
     if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
     max_pairs[dev] = n;
   }
-  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr};
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0};
+  if (sc) {
+    for (int i = 0; i < ARCQ_MAX_PEERS; ++i) p.peer_d[i] = (__nv_bfloat16 *)sc->peer_recv[i < sc->world ? i : sc->world - 1];
+    p.rs_rows = sc->rows_per_rank;
+    p.rs_rank = sc->rank;
+  }
 #ifdef ARCQ_GEMM_PROFILE
   static long long *prof_buf = nullptr;
   const bool do_prof = getenv("ARCQ_GEMM_PROF") != nullptr;
@@ -437,6 +454,14 @@ int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *
                      const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream) {
   if (swiglu) return launch_gemm_pair_t<true>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream);
   return launch_gemm_pair_t<false>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream);
+}
+
+// row-parallel GEMM whose epilogue IS the first half of the reduce-scatter (always the cta_group::2 kernel: any shape works)
+int launch_gemm_pair_scatter(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
+                             const float *alpha_dev, const float *col_scale, void *const *peer_recv, int world, int rank,
+                             int rows_per_rank, int64_t ldd, cudaStream_t stream) {
+  const ScatterArgs sc{peer_recv, world, rank, rows_per_rank};
+  return launch_gemm_pair_t<false>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, peer_recv[rank], ldd, stream, &sc);
 }
 
 }  // namespace arcq

@@ -186,7 +186,8 @@ class Layer:
                    cut into slabs and the collective of slab i runs on a communication stream under the GEMM of slab i+1;
       mode "tp-ar" plain all-reduce of the bf16 partials after o and down (activations replicated)."""
 
-    def __init__(self, torch, agemm, M, dev, workload="llama3-8b", seed=0, world=1, rank=0, sp=True, fused=True, slabs=1, swiglu=False):
+    def __init__(self, torch, agemm, M, dev, workload="llama3-8b", seed=0, world=1, rank=0, sp=True, fused=True, slabs=1, swiglu=False,
+                 dist=None, peer=False):
         import numpy as np
         from tests._util import make_acts
         from arcquant_b200 import tp
@@ -197,6 +198,12 @@ class Layer:
         if self.sp and M % (128 * world * self.slabs):
             raise SystemExit("bench.py: tokens must be a multiple of 128 * world * slabs for the sequence-parallel edges")
         self.items = []
+        self.dist = dist
+        # exchange over peer memory (arcquant_b200/peer.py, csrc/peer.cu): the row-parallel GEMM's epilogue scatters into the
+        # owners' receive slots and the codes are gathered by peer stores -- no NCCL kernel on the data path
+        self.peer, self.peer_note = None, None
+        if peer and self.sp and self.slabs == 1 and dist is not None:
+            self.peer, self.peer_note = self._peer_setup(dist, dev, world)
         g = torch.Generator().manual_seed(seed)
         for name, KQ, KE, Ns in layer_items(workload):
             xs, idx = make_acts(min(M, 256), KQ, KE, seed=seed + KQ)  # distribution A, pre-scaled
@@ -247,9 +254,52 @@ class Layer:
             if row and self.sp:
                 it["y_rs"] = [torch.empty((My, l[7]), dtype=torch.bfloat16, device=dev) for l in it["launches"]]
             self.items.append(it)
+        if self.peer is not None:
+            self.peer, self.peer_note = self._peer_buffers(dist, dev)
         if self.slabs > 1:
             self.comm = torch.cuda.Stream()
         torch.cuda.synchronize()
+
+    # -- peer-memory exchange: set-up (collective; every rank ends up on the same path) --
+    def _agree(self, dist, dev, ok):
+        flag = self.torch.tensor([1 if ok else 0], dtype=self.torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return bool(int(flag.item()))
+
+    def _peer_setup(self, dist, dev, world):
+        from arcquant_b200 import peer as P
+        grp, note = None, None
+        try:
+            if world > P.MAX_PEERS:
+                raise RuntimeError("more than %d ranks" % P.MAX_PEERS)
+            grp = P.PeerGroup(dist, dev).init_flags()
+        except Exception as e:  # noqa: BLE001
+            grp, note = None, "peer memory unavailable (%s): NCCL exchange" % str(e).splitlines()[0][:160]
+        if not self._agree(dist, dev, grp is not None):
+            return None, note or "peer memory unavailable on another rank: NCCL exchange"
+        return grp, None
+
+    def _peer_buffers(self, dist, dev):
+        """Gathered code / scale buffers and receive slots as peer-mapped allocations (replacing the torch ones)."""
+        from arcquant_b200 import peer as P
+        torch, W = self.torch, self.world
+        note = None
+        try:
+            for it in self.items:
+                K = it["KQ"] + it["KE"]
+                if it["gather"]:
+                    it["qx_pb"] = P.PeerBuffer(self.peer, it["qx_full"].numel())
+                    it["sfx_pb"] = P.PeerBuffer(self.peer, it["sfx_full"].numel())
+                    it["qx_full"] = it["qx_pb"].view(torch.uint8, it["qx_full"].shape)
+                    it["sfx_full"] = it["sfx_pb"].view(torch.uint8, it["sfx_full"].shape)
+                if it["reduce"]:
+                    My = self.M // W
+                    it["recv"] = [P.PeerBuffer(self.peer, P.world_bytes(W, My, l[7])) for l in it["launches"]]
+        except Exception as e:  # noqa: BLE001
+            note = "peer buffers unavailable (%s): NCCL exchange" % str(e).splitlines()[0][:160]
+        if not self._agree(dist, dev, note is None):
+            return None, note or "peer buffers unavailable on another rank: NCCL exchange"
+        return self.peer, None
 
     # -- one quantise launch + its GEMMs (+ the exchange steps of the tensor-parallel modes) --
     def _gemms(self, it, qx, sfx, rows=None, events=None):
@@ -278,10 +328,27 @@ class Layer:
             events.append(("quant", it["name"], it["KQ"], it["KE"], 0, x.shape[0], 0, e0, e1))
         if it["gather"]:  # every rank quantised its own tokens: gather the codes and the 128-row scale blocks
             full, mine = it["sf_valid"]
-            dist.all_gather_into_tensor(it["qx_full"], qx)
-            dist.all_gather_into_tensor(it["sfx_full"][:full], sfx[:mine])
+            if self.peer is not None:   # one kernel: peer stores of both segments + barrier (csrc/peer.cu)
+                self.peer.allgather(qx, it["qx_pb"], self.rank * qx.numel(), sfx[:mine], it["sfx_pb"], self.rank * mine, channel=1)
+            else:
+                dist.all_gather_into_tensor(it["qx_full"], qx)
+                dist.all_gather_into_tensor(it["sfx_full"][:full], sfx[:mine])
             qx, sfx = it["qx_full"], it["sfx_full"]
         it["last_q"] = (qx, sfx)
+        if it["reduce"] and self.peer is not None:
+            # row-parallel GEMM whose epilogue stores each 128-row block into its owner's receive slot over NVLink, then one
+            # barrier + local fp32 sum of the W slots: the whole reduce-scatter, without a collective kernel
+            outs, My = [], self.M // self.world
+            for j, (label, N, qw, sfw, alpha, cs, epi, out_cols) in enumerate(it["launches"]):
+                if events is not None:
+                    e0 = torch.cuda.Event(enable_timing=True); e0.record()
+                self.peer.gemm_scatter(qx, qw, sfx, sfw, alpha, it["recv"][j], My, col_scale=cs)
+                if events is not None:
+                    e1 = torch.cuda.Event(enable_timing=True); e1.record()
+                    events.append(("gemm", label + "+scatter", it["KQ"], it["KE"], N, qx.shape[0], out_cols, e0, e1))
+                self.peer.reduce(it["recv"][j], My, N, it["y_rs"][j], channel=0)
+                outs.append(it["y_rs"][j])
+            return outs
         outs = self._gemms(it, qx, sfx, None, events)
         if it["reduce"]:
             for j, y in enumerate(outs):
@@ -458,6 +525,7 @@ class Layer:
             for j, (label, N, qw, sfw, alpha, cs, epi, out_cols) in enumerate(it["launches"]):
                 ref, mag = T.gemm_rows(qx, sfx, qw, sfw, grows, alpha, cs)
                 y = it["y"][j]
+                peer_rs = it["reduce"] and self.peer is not None   # the partial never existed locally: it sits in the owners' slots
                 if epi == self.agemm.EPILOGUE_SWIGLU:
                     nb = N // 256
                     r3 = ref.view(-1, nb, 2, 128)
@@ -465,10 +533,20 @@ class Layer:
                     got = y[grows].double()
                     res["swiglu_rel_err_max"] = max(res["swiglu_rel_err_max"], float((got - want).norm() / want.norm().clamp_min(1e-30)))
                 else:
-                    got = y[grows].double()
                     tol = 2.0 ** -8 * ref.abs() + 2.0 ** -18 * mag + 1e-30
+                    if peer_rs:   # this rank's partial of the rows it owns = its own slot of its own receive buffer
+                        mine = self._rs_rows(grows)
+                        if mine is not None:
+                            sel, local = mine
+                            My = self.M // W
+                            slot = it["recv"][j].view(torch.bfloat16, (W, My, N))[self.rank]
+                            got_p = slot[local].double()
+                            res["gemm_max_err_over_tol"] = max(res["gemm_max_err_over_tol"], float(((got_p - ref[sel]).abs() / tol[sel]).max()))
+                            res["gemm_rel_fro_max"] = max(res["gemm_rel_fro_max"], float((got_p - ref[sel]).norm() / ref[sel].norm().clamp_min(1e-30)))
+                    else:
+                        got = y[grows].double()
                     in_place_sum = it["reduce"] and not self.sp   # tp-ar: y already holds the all-reduced sum, not the partial
-                    if not in_place_sum:
+                    if not in_place_sum and not peer_rs:
                         res["gemm_max_err_over_tol"] = max(res["gemm_max_err_over_tol"], float(((got - ref).abs() / tol).max()))
                         res["gemm_rel_fro_max"] = max(res["gemm_rel_fro_max"], float((got - ref).norm() / ref.norm().clamp_min(1e-30)))
                     if it["reduce"]:
@@ -494,7 +572,13 @@ class Layer:
             dist.all_reduce(c)
             res["gemm_max_err_over_tol"], res["gemm_rel_fro_max"], res["swiglu_rel_err_max"], res["tp_reduce_max_err_over_tol"] = t.tolist()
             res["quant_bytes_differ"], res["tp_gather_bytes_differ"] = (int(v) for v in c.tolist())
-        res["ok"] = bool(res["quant_bytes_differ"] == 0 and res["tp_gather_bytes_differ"] == 0 and res["gemm_max_err_over_tol"] <= 1.0
+        if self.peer is not None:
+            try:
+                self.peer.status()
+                res["peer_barrier_timeouts"] = 0
+            except RuntimeError:
+                res["peer_barrier_timeouts"] = 1
+        res["ok"] = bool(res.get("peer_barrier_timeouts", 0) == 0 and res["quant_bytes_differ"] == 0 and res["tp_gather_bytes_differ"] == 0 and res["gemm_max_err_over_tol"] <= 1.0
                          and res["gemm_rel_fro_max"] < 2e-3 and res["swiglu_rel_err_max"] < 1e-2 and res["tp_reduce_max_err_over_tol"] <= 1.0)
         return res
 
@@ -530,7 +614,8 @@ def run_native(args):
     tp_mode = world > 1 and args.parallelism in ("tp", "tp-ar")
     slabs = args.slabs if (tp_mode and args.parallelism == "tp") else 1
     layer = Layer(torch, agemm, M, dev, workload=args.workload, world=world if tp_mode else 1, rank=rank if tp_mode else 0,
-                  sp=args.parallelism == "tp", fused=not args.unfused, slabs=slabs, swiglu=args.swiglu and not args.unfused)
+                  sp=args.parallelism == "tp", fused=not args.unfused, slabs=slabs, swiglu=args.swiglu and not args.unfused,
+                  dist=dist if tp_mode else None, peer=args.peer and tp_mode and args.parallelism == "tp" and slabs == 1)
     layer.dist = dist
 
     def barrier():
@@ -538,6 +623,18 @@ def run_native(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    if layer.peer is not None:
+        # first step on the peer-memory path: if any barrier timed out (a rank that cannot see its peers' stores), every rank
+        # drops to the NCCL exchange together instead of timing a broken step
+        layer.step()
+        torch.cuda.synchronize()
+        try:
+            layer.peer.status()
+            ok = True
+        except RuntimeError as e:
+            ok, layer.peer_note = False, "peer barrier timed out in the first step (%s): NCCL exchange" % str(e)[:120]
+        if not layer._agree(dist, dev, ok):
+            layer.peer, layer.peer_note = None, layer.peer_note or "peer barrier timed out on another rank: NCCL exchange"
     for _ in range(max(args.warmup, 3)):
         layer.step()
     barrier()
@@ -734,11 +831,13 @@ def run_native(args):
                                    else "weak: %d tokens per GPU (replicas)" % M,
                    "parallelism": ("tp%d: qkv/gate/up column-parallel, o/down row-parallel (ARC columns with their shard); %s; "
                                    "%d slab(s), collectives on a communication stream under the next slab's kernels; step %s; "
-                                   "%d bytes per rank per step into NCCL" % (
+                                   "%d bytes per rank per step %s" % (
                                        world, "reduce-scatter of bf16 partials + all-gather of NVFP4 codes/scales (sequence-parallel edges)"
                                        if layer.sp else "all-reduce of bf16 partials", layer.slabs,
                                        "replayed from a CUDA graph" if graph is not None else "launched from Python",
-                                       layer.exchange_bytes())) if tp_mode
+                                       layer.exchange_bytes(),
+                                       "over PEER MEMORY (NVLink P2P stores from the GEMM epilogue / gather kernel + flag barriers; no NCCL kernel "
+                                       "on the data path)" if layer.peer is not None else "into NCCL")) if tp_mode
                    else ("replicas (token-parallel), no collective" if world > 1 else "single GPU")},
         "tokens_per_s_linear_path": (M if (tp_mode or world == 1) else world * M) * args.steps / (ms_max * 1e-3),
         "e2e": {"value": e2e_val, "unit": "TFLOP/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -748,6 +847,10 @@ def run_native(args):
         "parity_check": parity, "cpu_baseline": cpu, "clocks": clocks, "prefill_config3": prefill_res,
         "binding": agemm.BACKEND,
     }
+    if tp_mode:
+        out["exchange"] = "peer" if layer.peer is not None else "nccl"
+        if layer.peer_note:
+            out["exchange_note"] = layer.peer_note
     print(json.dumps(out))
     _leave(world)
 
@@ -807,6 +910,11 @@ def main():
                          "which also replaces the callers' torch SiLU*up pass and halves the bytes written)")
     ap.set_defaults(swiglu=True)
     ap.add_argument("--no-graph", action="store_true", help="(default) tp: launch from Python")
+    ap.add_argument("--no-peer", dest="peer", action="store_false",
+                    help="tp: exchange through NCCL (reduce_scatter_tensor + all_gather_into_tensor) instead of the peer-memory path "
+                         "(GEMM epilogue scatters into the owners' receive slots over NVLink + barrier/fp32-sum kernel; codes gathered by "
+                         "peer stores), which is the default when the ranks can map each other's memory")
+    ap.set_defaults(peer=True)
     ap.add_argument("--no-check", action="store_true", help="skip the oracle check of the last step's outputs")
     ap.add_argument("--no-prefill", action="store_true", help="skip the config-3 prefill line (N=1)")
     ap.add_argument("--e2e-steps", type=int, default=5)

@@ -148,6 +148,58 @@ int arcq_linear_noalloc(const void *x, int64_t M, int KQ, const int16_t *idx, in
                         const void *qw, const void *sfw, int64_t N, float alpha, const float *alpha_dev,
                         void *y, void *stream);
 
+/* ---- Tensor-parallel exchange over peer memory (NVLink / NVSwitch P2P), SURVEY.md §8 f4 ---------------------------------
+ * NO COUNTERPART IN THE REFERENCE (it has no distributed code): these replace this repo's own NCCL data plane
+ * for the sharding the north star names (o_proj / down_proj split K over ranks, tokens reduce-scattered; the inputs of
+ * the column-parallel linears all-gathered as NVFP4 codes + scale blocks).  csrc/peer.cu, csrc/gemm_pair.cu.
+ *
+ * Memory: arcq_peer_alloc = zeroed cudaMalloc memory (exportable; a caching allocator's sub-allocations are not);
+ * arcq_peer_export / _open / _close move it between the processes of one node as a 64-byte CUDA IPC handle (the caller
+ * carries the bytes, e.g. torch.distributed.all_gather_object); arcq_peer_enable is the single-process-several-GPUs
+ * equivalent (cudaDeviceEnablePeerAccess).  Every `peer_*` argument below is a HOST array of `world` DEVICE pointers,
+ * entry r = rank r's buffer as mapped into THIS process (entry `rank` = the local buffer).
+ *
+ * Flag block: ARCQ_PEER_FLAG_BYTES of zeroed peer memory per rank, shared by all calls of one communicator; `channel`
+ * (< ARCQ_PEER_CHANNELS) separates barriers that may be in flight at the same time (one per stream is enough).  The
+ * barrier epoch lives in the flag block, not in a host counter, so launches replay from CUDA graphs.  Waits are bounded
+ * (4 s): a rank that never arrives makes the kernel finish with a sticky error that arcq_peer_status reports
+ * (ARCQ_ECUDA) -- it does not hang the GPU.
+ *
+ *   arcq_gemm_nvfp4_scatter  arcq_gemm_nvfp4_ex (EPILOGUE_NONE) whose epilogue stores the 128-row block starting at row g
+ *       into peer_recv[g / rows_per_rank] at row (rank * rows_per_rank + g % rows_per_rank): rank o's receive buffer is
+ *       bf16 [world][rows_per_rank][ldd], slot s = rank s's partial of the rows o owns.  The stores leave tile by tile
+ *       under the math of the next tile; there is no partial-sum buffer in local HBM and no collective kernel.
+ *       rows_per_rank % 128 == 0, rows_per_rank * world >= M.
+ *   arcq_peer_reduce         cross-GPU barrier (every rank's scatter GEMM, launched before it on the same stream, has
+ *       finished), then out[r, c] = bf16(sum_s fp32(recv_local[s][r][c])), s ascending: deterministic, one rounding
+ *       (NCCL's ring rounds to bf16 per hop).  cols % 8 == 0.
+ *   arcq_peer_allgather      copies up to two local segments (bytes1 = 0: one) to byte offset dst_off of every rank's
+ *       destination buffer, then the same barrier: when the kernel completes, every rank's segments have landed here.
+ *       Sizes / offsets multiples of 16.  (codes: offset rank * Mx * K/2; scale blocks: rank * Mx * K/16.)
+ * Buffer reuse is the caller's contract: a receive / gather buffer may be overwritten by a peer as soon as that peer has
+ * passed a barrier that this rank entered AFTER its last read of the buffer (in a layer that alternates these calls this
+ * always holds; otherwise alternate two buffers). */
+#define ARCQ_MAX_PEERS 8
+#define ARCQ_PEER_HANDLE_BYTES 64
+#define ARCQ_PEER_FLAG_BYTES 4096
+#define ARCQ_PEER_CHANNELS 32
+int arcq_peer_alloc(int64_t bytes, void **ptr_out);
+int arcq_peer_free(void *ptr);
+int arcq_peer_export(void *ptr, void *handle_out);
+int arcq_peer_open(const void *handle, void **ptr_out);
+int arcq_peer_close(void *ptr);
+int arcq_peer_enable(int peer_device);
+int arcq_peer_status(const void *flags_local, void *stream);
+int arcq_gemm_nvfp4_scatter(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
+                            int64_t K, float alpha, const float *alpha_dev, const float *col_scale_dev,
+                            void *const *peer_recv, int world, int rank, int64_t rows_per_rank, int64_t ldd,
+                            void *stream);
+int arcq_peer_reduce(const void *recv_local, void *const *peer_flags, int world, int rank, int channel, int64_t rows,
+                     int64_t cols, int64_t ld, void *out, int64_t ldo, void *stream);
+int arcq_peer_allgather(const void *src0, int64_t bytes0, void *const *peer_dst0, int64_t dst_off0, const void *src1,
+                        int64_t bytes1, void *const *peer_dst1, int64_t dst_off1, void *const *peer_flags, int world,
+                        int rank, int channel, void *stream);
+
 /* name = value override of a shape-driven kernel choice ("" = back to the default).  Every choice computes the same
  * result; the parity tests force each tile organisation through this.  Options: "quant_tile" = "R,threads,S,RT,CTAs/SM",
  * "quant_family" = 3 | 1, "gemm_pair" = 0 | 1, "gemm_bn" = 128 | 256, "gemm_splitk" = 0 | 2 | 4 | 8.  The product

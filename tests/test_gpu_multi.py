@@ -34,7 +34,9 @@ def _need2():
 
 
 @pytest.mark.parametrize("args", [
-    ["--parallelism", "tp"],                                   # default: one slab, launched from Python
+    ["--parallelism", "tp"],                                   # default: exchange over peer memory (CUDA IPC), one slab, from Python
+    ["--parallelism", "tp", "--graph"],                        # the same, replayed from a CUDA graph (device-resident barrier epochs)
+    ["--parallelism", "tp", "--no-peer"],                      # NCCL reduce-scatter + all-gather
     ["--parallelism", "tp", "--slabs", "2", "--graph"],        # micro-batch slabs on a communication stream, CUDA-graph replay
     ["--parallelism", "tp", "--slabs", "4", "--unfused"],
     ["--parallelism", "tp-ar"],
@@ -61,6 +63,10 @@ def test_two_rank_step_parity(args):
     assert pc["ranks"] == 2 and pc["ok"], pc
     assert pc["quant_bytes_differ"] == 0 and pc["tp_gather_bytes_differ"] == 0
     assert out["n_gpus"] == 2 and out["gpu_launches"] > 0 and out["scaling"] == "strong"
+    peer_expected = "--no-peer" not in args and "--slabs" not in args and "tp-ar" not in args
+    assert out["exchange"] == ("peer" if peer_expected else "nccl"), out.get("exchange_note")
+    if peer_expected:
+        assert pc["peer_barrier_timeouts"] == 0
 
 
 def test_two_devices_from_one_process():
