@@ -329,7 +329,12 @@ class Layer:
         if it["gather"]:  # every rank quantised its own tokens: gather the codes and the 128-row scale blocks
             full, mine = it["sf_valid"]
             if self.peer is not None:   # one kernel: peer stores of both segments + barrier (csrc/peer.cu)
+                if events is not None:
+                    e0 = torch.cuda.Event(enable_timing=True); e0.record()
                 self.peer.allgather(qx, it["qx_pb"], self.rank * qx.numel(), sfx[:mine], it["sfx_pb"], self.rank * mine, channel=1)
+                if events is not None:
+                    e1 = torch.cuda.Event(enable_timing=True); e1.record()
+                    events.append(("xchg", "peer_allgather " + it["name"], it["KQ"], it["KE"], 0, x.shape[0], (qx.numel() + mine) * self.world, e0, e1))
             else:
                 dist.all_gather_into_tensor(it["qx_full"], qx)
                 dist.all_gather_into_tensor(it["sfx_full"][:full], sfx[:mine])
@@ -347,6 +352,9 @@ class Layer:
                     e1 = torch.cuda.Event(enable_timing=True); e1.record()
                     events.append(("gemm", label + "+scatter", it["KQ"], it["KE"], N, qx.shape[0], out_cols, e0, e1))
                 self.peer.reduce(it["recv"][j], My, N, it["y_rs"][j], channel=0)
+                if events is not None:
+                    e2 = torch.cuda.Event(enable_timing=True); e2.record()
+                    events.append(("xchg", "peer_reduce " + label, it["KQ"], it["KE"], N, My, (self.world + 1) * My * N * 2, e1, e2))
                 outs.append(it["y_rs"][j])
             return outs
         outs = self._gemms(it, qx, sfx, None, events)
@@ -645,7 +653,9 @@ def run_native(args):
     # tensor-parallel shards are launch-bound (a few hundred microseconds of kernels against ~20 host calls): capture the
     # step (kernels + NCCL collectives, both streams) in a CUDA graph and replay it
     graph = None
-    if tp_mode and args.graph and not args.no_graph:
+    # default with the peer-memory exchange: the captured step then holds only this library's kernels (no NCCL node), and at
+    # N >= 4 a shard's kernels are shorter than the ~20 host calls that launch them
+    if tp_mode and (args.graph or layer.peer is not None) and not args.no_graph:
         ok = 1
         try:
             side = torch.cuda.Stream()
@@ -760,6 +770,9 @@ def run_native(args):
                 k["ref_kernel_us"] = r["ref_kernel_us_best"]
                 k["speedup_vs_ref_kernel"] = r["ref_kernel_us_best"] / (1e3 * avg)
             kernels.append(k)
+        elif kind == "xchg":   # barrier wait (rank skew) included; bytes = what the kernel reads + writes
+            kernels.append({"kernel": label.split()[0], "of": label.split()[1], "rows": rows, "us": 1e3 * avg, "calls_per_step": calls_per_step,
+                            "bytes": out_cols, "GBps": out_cols / (avg * 1e-3) / 1e9})
         else:
             fl = 2.0 * rows * N * (KQ + KE)
             kernels.append({"kernel": "gemm", "launch": label, "N": N, "K": KQ + KE, "rows": rows, "us": 1e3 * avg,
@@ -903,13 +916,14 @@ def main():
                     help="tp: token slabs (micro-batches) whose collectives run on a communication stream under the other slabs' "
                          "kernels; measured SLOWER than 1 at N=2 (0.97 vs 0.83 ms: split GEMMs + NCCL kernels taking SMs from the "
                          "persistent GEMM grid), so off by default")
-    ap.add_argument("--graph", action="store_true", help="tp: capture the step (kernels + NCCL) in a CUDA graph and replay it")
+    ap.add_argument("--graph", action="store_true", help="tp: capture the step in a CUDA graph and replay it (default with the peer-memory "
+                                                         "exchange; with --no-peer the graph also holds the NCCL collectives)")
     ap.add_argument("--unfused", action="store_true", help="7 GEMM launches per step (the reference's launch structure)")
     ap.add_argument("--no-swiglu", dest="swiglu", action="store_false",
                     help="keep gate and up as two plain launches (default: ONE launch whose epilogue writes bf16(silu(gate)) * up, "
                          "which also replaces the callers' torch SiLU*up pass and halves the bytes written)")
     ap.set_defaults(swiglu=True)
-    ap.add_argument("--no-graph", action="store_true", help="(default) tp: launch from Python")
+    ap.add_argument("--no-graph", action="store_true", help="tp: launch every step from Python")
     ap.add_argument("--no-peer", dest="peer", action="store_false",
                     help="tp: exchange through NCCL (reduce_scatter_tensor + all_gather_into_tensor) instead of the peer-memory path "
                          "(GEMM epilogue scatters into the owners' receive slots over NVLink + barrier/fp32-sum kernel; codes gathered by "
