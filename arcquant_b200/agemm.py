@@ -28,7 +28,7 @@ import torch
 from . import _lib
 
 __all__ = [
-    "matmul", "reorder_quantize_x", "reorder_quantize_w", "rmsnorm_quantize_x", "reorder_quantize_x_scaled", "absmax",
+    "matmul", "reorder_quantize_x", "reorder_quantize_w", "rmsnorm_quantize_x", "add_rmsnorm_quantize_x", "reorder_quantize_x_scaled", "absmax",
     "sf_bytes", "flavour_for_kq", "launch_count", "set_option", "use_plans", "fuse_weights", "interleave_gate_up",
     "EPILOGUE_NONE", "EPILOGUE_SWIGLU", "PRESCALE_FP32", "PRESCALE_BF16_DIVISOR", "FLAVOUR_16", "FLAVOUR_32", "BACKEND",
 ]
@@ -152,6 +152,31 @@ def _c_rmsnorm_quantize_x(X, W, eps, reorder_index, KE):
     return q, sf
 
 
+def _c_add_rmsnorm_quantize_x(X, residual, W, eps, reorder_index, KE):
+    """residual + hidden_states, then the norm + quantise of the next block, in one launch (modeling_arc.py:294-301):
+    returns (QX, SFX, X + residual)."""
+    L = _lib.load()
+    _need(X, "X", torch.bfloat16, 2)
+    _need(residual, "residual", torch.bfloat16, 2)
+    _need(W, "W", torch.bfloat16, 1)
+    _need(reorder_index, "reorder_index", torch.int16, 1)
+    M, H = X.shape
+    if tuple(residual.shape) != (M, H) or W.numel() != H or reorder_index.numel() != H:
+        raise RuntimeError("residual must have the shape of X; W and reorder_index must have %d entries" % H)
+    if W.device != X.device or reorder_index.device != X.device or residual.device != X.device:
+        raise RuntimeError("all inputs must be on %s" % X.device)
+    KE = int(KE)
+    K = H + KE
+    with torch.cuda.device(X.device):
+        q = torch.empty((M, K // 2), dtype=torch.uint8, device=X.device)
+        sf = torch.empty((_sf_bytes(M, K),), dtype=torch.uint8, device=X.device)
+        s = torch.empty((M, H), dtype=torch.bfloat16, device=X.device)
+        rc = L.arcq_add_rmsnorm_quantize_x(X.data_ptr(), residual.data_ptr(), W.data_ptr(), float(eps), M, H, reorder_index.data_ptr(),
+                                           KE, s.data_ptr(), q.data_ptr(), sf.data_ptr(), _stream(X))
+    _lib.check(rc, "arcq_add_rmsnorm_quantize_x")
+    return q, sf, s
+
+
 def _c_matmul(A, B, SFA, SFB, scale, col_scale=None, epilogue: int = 0, out=None):
     """nvfp4 matmul, return bfloat16 tensor (bindings.cpp:99-120): scale * (A.SFA) @ (B.SFB)^T."""
     L = _lib.load()
@@ -219,6 +244,7 @@ if _ext is not None:
     reorder_quantize_x = _ext.reorder_quantize_x
     reorder_quantize_w = _ext.reorder_quantize_w
     rmsnorm_quantize_x = _ext.rmsnorm_quantize_x
+    add_rmsnorm_quantize_x = _ext.add_rmsnorm_quantize_x
     reorder_quantize_x_scaled = _ext.reorder_quantize_x_scaled
     absmax = _ext.absmax
     sf_bytes = _ext.sf_bytes
@@ -237,6 +263,7 @@ else:
     reorder_quantize_x = _c_reorder_quantize_x
     reorder_quantize_w = _c_reorder_quantize_w
     rmsnorm_quantize_x = _c_rmsnorm_quantize_x
+    add_rmsnorm_quantize_x = _c_add_rmsnorm_quantize_x
     reorder_quantize_x_scaled = _c_reorder_quantize_x_scaled
     absmax = _c_absmax
     sf_bytes = _c_sf_bytes

@@ -116,6 +116,28 @@ std::tuple<torch::Tensor, torch::Tensor> rmsnorm_quantize_x(const torch::Tensor 
   return std::make_tuple(Q, SF);
 }
 
+// residual + hidden_states, then the norm + quantise of the next block, in one launch: returns (QX, SFX, sum)
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> add_rmsnorm_quantize_x(const torch::Tensor &X, const torch::Tensor &residual, const torch::Tensor &W,
+                                                                               float eps, const torch::Tensor &reorder_index, int KE) {
+  need(X, "X", torch::kBFloat16, 2);
+  need(residual, "residual", torch::kBFloat16, 2);
+  need(W, "W", torch::kBFloat16, 1);
+  need(reorder_index, "reorder_index", torch::kInt16, 1);
+  const int64_t M = X.size(0), H = X.size(1), K = H + KE;
+  TORCH_CHECK(residual.size(0) == M && residual.size(1) == H, "residual must have the shape of X");
+  TORCH_CHECK(W.numel() == H && reorder_index.numel() == H, "W and reorder_index must have ", H, " entries");
+  TORCH_CHECK(W.device() == X.device() && reorder_index.device() == X.device() && residual.device() == X.device(), "all inputs must be on ", X.device());
+  const c10::cuda::CUDAGuard guard(X.device());
+  auto opt = torch::dtype(torch::kUInt8).device(X.device());
+  auto Q = torch::empty({M, K / 2}, opt);
+  auto SF = torch::empty({sf_bytes(M, K)}, opt);
+  auto S = torch::empty({M, H}, torch::dtype(torch::kBFloat16).device(X.device()));
+  fail(arcq_add_rmsnorm_quantize_x(X.data_ptr(), residual.data_ptr(), W.data_ptr(), eps, M, (int)H, reorder_index.data_ptr<int16_t>(), KE, S.data_ptr(),
+                                   Q.data_ptr(), SF.data_ptr(), stream_of(X)),
+       "arcq_add_rmsnorm_quantize_x");
+  return std::make_tuple(Q, SF, S);
+}
+
 // max|x| of a bf16 tensor as a 1-element fp32 CUDA tensor (no host sync)
 torch::Tensor absmax(const torch::Tensor &X) {
   need(X, "X", torch::kBFloat16);
@@ -220,6 +242,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         py::arg("reorder_index"), py::arg("KE"), py::arg("flavour") = -1);
   m.def("rmsnorm_quantize_x", &rmsnorm_quantize_x, "Rmsnorm and quantize activation, return K + KE channels", py::arg("X"), py::arg("W"),
         py::arg("eps"), py::arg("reorder_index"), py::arg("KE"));
+  m.def("add_rmsnorm_quantize_x", &add_rmsnorm_quantize_x,
+        "residual add fused in front of rmsnorm_quantize_x (modeling_arc.py:294-301): (QX, SFX, X + residual)", py::arg("X"), py::arg("residual"),
+        py::arg("W"), py::arg("eps"), py::arg("reorder_index"), py::arg("KE"));
   m.def("reorder_quantize_x_scaled", &reorder_quantize_x_scaled,
         "max|x| / 2688 pre-scale fused into reorder_quantize_x (NVFP4_reorder_quantize_x of the reference callers): (QX, SFX, scale)",
         py::arg("X"), py::arg("reorder_index"), py::arg("KE"), py::arg("flavour") = -1, py::arg("amax") = py::none(), py::arg("mode") = 0);

@@ -449,3 +449,22 @@ extern "C" int arcq_rmsnorm_quantize_x(const void *x, const void *w, float eps, 
     default: return launch_quant<1, 0, false, true>(p, st);
   }
 }
+
+// residual add fused in front of rmsnorm_quantize_x: h = bf16(x + res) -> sum_out, (qx, sfx) = rmsnorm_quantize_x(h)
+extern "C" int arcq_add_rmsnorm_quantize_x(const void *x, const void *res, const void *w, float eps, int64_t M, int H,
+                                           const int16_t *idx, int KE, void *sum_out, void *qx, void *sfx, void *stream) {
+  if (int rc = check_common(x, M, H, idx, KE, ARCQ_FLAVOUR_16, qx, sfx)) return rc;
+  if (!w || ((uintptr_t)w & 15)) { set_error("rmsnorm weight must be a 16-byte aligned device pointer"); return ARCQ_EINVAL; }
+  if (!res || !sum_out || (((uintptr_t)res | (uintptr_t)sum_out) & 15)) {
+    set_error("arcq_add_rmsnorm_quantize_x: res and sum_out must be 16-byte aligned device pointers");
+    return ARCQ_EINVAL;
+  }
+  if (H < 2048 || H > 8192) { set_error("rmsnorm_quantize_x supports 2048 <= H <= 8192, got %d", H); return ARCQ_ENOSUP; }
+  if (M == 0) return ARCQ_OK;
+  QuantParams p{(const uint16_t *)x, idx, (const uint16_t *)w, (uint8_t *)qx, (uint8_t *)sfx, nullptr, nullptr, nullptr, 0, eps, (int)M, H, KE, 0, 0,
+                (const uint16_t *)res, (uint16_t *)sum_out};
+  const int rc = launch_quant_tma(p, ARCQ_FLAVOUR_16, false, true, (cudaStream_t)stream);
+  if (rc == ARCQ_ENOSUP) set_error("arcq_add_rmsnorm_quantize_x: H=%d KE=%d is outside the TMA-staged kernel's shapes (H, KE multiples of 64); add separately", H, KE);
+  return rc;
+}
+

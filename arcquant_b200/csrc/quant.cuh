@@ -18,6 +18,9 @@ struct QuantParams {
   int M, KQ, KE;
   int num_tiles;
   int debug;  // -DARCQ_EXPERIMENT builds only: 1 skip transpose, 2 skip gather, 4 skip quantise math, 8 skip residuals
+  // ADD (rmsnorm only): the normalised input is h = bf16(x + res); h is also written to sum_out (the new residual stream)
+  const uint16_t *res;   // bf16 [M, KQ] (nullable = no add)
+  uint16_t *sum_out;     // bf16 [M, KQ]
 };
 
 constexpr float kFp4Max = 6.0f;            // reorder.cu:17

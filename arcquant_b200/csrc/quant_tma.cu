@@ -34,7 +34,10 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     const int *q = options().quant_tile;
     if (q[0] > 0) c = Cfg{q[0], q[1], q[4], q[2], q[3]};
   }
-  const bool want_plan = p.plan != nullptr && !rms && !is_w;
+  const bool add = rms && p.res != nullptr;   // fused residual add: second set of staging slots, register transposition
+  // (the rmsnorm variant on the planned path -- sum of squares in a pass of its own -- measured 36.5 us against 32.8 us
+  // for the register transposition at 8192 x 4096, profiles/r2_quant_rms_plan_ab.log: it stays unplanned)
+  const bool want_plan = p.plan != nullptr && !is_w && !rms;
   // with a plan the gather is conflict-free at any chunk width, which was the 8-row tile's advantage: for KQ <= 4096 the
   // 4-row tile at two CTAs per SM with ONE staging slot is then 3-4 % faster (profiles/r2_quant_tile_ab.log)
   const bool prefer4 = want_plan && ngroups <= 256 && plan_usable(4, p.KQ);
@@ -46,7 +49,7 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
       if (k.R == 4 && k.threads == 256 && ngroups > 256) continue;   // two passes per tile: the wide CTA owns its items
       // a placement plan is an extra: the tile organisation is chosen as if there were none, and the plan is used only
       // if it still fits next to it (below); it must never push the choice to a smaller tile
-      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S).total + 1024;
+      const int need = carve_t(k.R, p.KQ, p.KE, rms, false, k.S, false, false, add).total + 1024;
       if (need * k.minb > kSmemPerSm) continue;
       if (blocks * (128 / k.R) < (int64_t)sms * k.minb && k.R > 1) continue;
       c = k;
@@ -65,8 +68,8 @@ int launch_quant_tma(const QuantParams &p, int flavour, bool is_w, bool rms, cud
     else planned = own2 = false;
   }
   pp.plan = planned ? p.plan + (int64_t)plan_section(c.R) * 2 * p.KQ : nullptr;   // this tile height's section
-  tab32 = !own && !planned && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S).total + 1024) * c.minb <= kSmemPerSm;
-  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned, own2).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
+  tab32 = !own && !planned && (carve_t(c.R, p.KQ, p.KE, rms, true, c.S, false, false, add).total + 1024) * c.minb <= kSmemPerSm;
+  if ((carve_t(c.R, p.KQ, p.KE, rms, tab32, c.S, planned, own2, add).total + 1024) * c.minb > kSmemPerSm) return ARCQ_ENOSUP;
 #define ARCQ_T(RR, RTT, TH, MB) \
   if (c.R == RR && c.RT == RTT && c.threads == TH && c.minb == MB) \
     return launch_tma_cfg_##RR##_##RTT##_##TH##_##MB(pp, flavour, is_w, rms, c.S, tab32, own, stream, own2);

@@ -37,7 +37,8 @@ struct CarveT {  // shared-memory layout (bytes), computed identically on host a
 // bytes added to every staged row: the 8 row addresses of one ldmatrix must fall into 8 different 16-byte bank groups.
 // Plan mode reads (two tile rows) x (four 8-channel blocks) per matrix: the odd tile row must sit 64 bytes off.
 __host__ __device__ constexpr int stage_pad_of(int R, bool plan) { return plan ? 64 : stage_pad(R); }
-__host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool tab32, int S, bool plan = false, bool own2 = false) {
+__host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool tab32, int S, bool plan = false, bool own2 = false,
+                                          bool add = false) {
   CarveT c;
   int o = 128;                  // mbarriers full[S] (S <= 4)
   c.lut = o; o += 2 * 128 * 4;  // rcp + sf LUTs
@@ -58,7 +59,7 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
   o = (o + 127) & ~127;
   c.tile = o; o += KQ * 2 * R;
   if (own2) c.tab = c.tile;
-  c.stage = o; o += S * (KQ * 2 + stage_pad_of(R, plan)) * R;
+  c.stage = o; o += (add ? 2 : 1) * S * (KQ * 2 + stage_pad_of(R, plan)) * R;   // add: the residual rows land in a second set of slots
   c.total = o;
   return c;
 }
@@ -68,7 +69,12 @@ __host__ __device__ inline CarveT carve_t(int R, int KQ, int KE, bool rms, bool 
 // OWN2: every thread owns up to TWO 16-groups (KQ/16 <= 2 * THREADS) and keeps their 32 gather offsets packed in 16
 // registers, so the per-tile loads of the offset table (a third of the gather's shared-memory traffic for 2-row tiles)
 // disappear and the table's shared memory goes to a second staging slot
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN, bool OWN2 = false>
+// ADD (rmsnorm, unplanned): h = bf16(x + res) replaces x -- the residual rows are staged by TMA next to the x rows, the add
+// happens in the registers of the transposing pass (which already holds whole 16-byte units of every row), h leaves for
+// sum_out from there and the sum of squares is taken from h: `residual + hidden_states` followed by the norm
+// (benchmarks/modeling_arc.py:294-301, model/qLlamaLayer.py:162-166) in one pass over the data
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN, bool OWN2 = false,
+          bool ADD = false>
 __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantParams p, const int S) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int CB = 2 * R;        // bytes of one channel chunk
@@ -82,7 +88,8 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
   const int G = (KQ - KE) / 16, ngroups = KQ / 16, nunits = KQ / 8, nchunks = K / 64;
   static_assert(!PLAN || (!RMS && (R == 8 || R == 4 || R == 2)), "plans exist for the matrix-transposed tiles");
   static_assert(!OWN2 || (PLAN && !OWN && !TAB32 && R == RT), "two owned groups per thread: planned, one row block per tile");
-  const CarveT cv = carve_t(R, KQ, KE, RMS, TAB32, S, PLAN, OWN2);
+  static_assert(!ADD || (RMS && !PLAN && !IS_W), "the residual add rides on the register transposition of the rmsnorm variant");
+  const CarveT cv = carve_t(R, KQ, KE, RMS, TAB32, S, PLAN, OWN2, ADD);
   uint64_t *full = reinterpret_cast<uint64_t *>(smem);
   float *rcp_lut = reinterpret_cast<float *>(smem + cv.lut), *sf_lut = rcp_lut + 128;
   const int sfs_bytes = nchunks * 4 * R;
@@ -114,11 +121,19 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     const uint8_t *src = reinterpret_cast<const uint8_t *>(p.x) + (int64_t)r0 * rowbytes;
     uint8_t *dst = stage + (size_t)s * slot_bytes;
     if (ptx::elect_one()) {
-      ptx::mbar_arrive_expect_tx(&full[s], (uint32_t)nv * rowbytes);
+      ptx::mbar_arrive_expect_tx(&full[s], (uint32_t)nv * rowbytes * (ADD ? 2u : 1u));
 #pragma unroll
       for (int lr = 0; lr < R; ++lr)
         if (TileMap<R>::row(0, lr) < mrows)
           ptx::bulk_load(dst + (size_t)lr * rowstride, src + (size_t)TileMap<R>::row(0, lr) * rowbytes, rowbytes, &full[s]);
+      if constexpr (ADD) {
+        const uint8_t *rsrc = reinterpret_cast<const uint8_t *>(p.res) + (int64_t)r0 * rowbytes;
+        uint8_t *rdst = dst + (size_t)S * slot_bytes;
+#pragma unroll
+        for (int lr = 0; lr < R; ++lr)
+          if (TileMap<R>::row(0, lr) < mrows)
+            ptx::bulk_load(rdst + (size_t)lr * rowstride, rsrc + (size_t)TileMap<R>::row(0, lr) * rowbytes, rowbytes, &full[s]);
+      }
     }
     __syncwarp();
   };
@@ -134,7 +149,7 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
     if (tid == 0) { ptx::mbar_init(plan_bar, 1); ptx::fence_barrier_init(); }
   }
   if (p.M % 128) {  // a ragged last block leaves rows of some slots unwritten: give them defined (zero) content
-    for (int i = tid; i < S * slot_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < (ADD ? 2 : 1) * S * slot_bytes / 16; i += THREADS) reinterpret_cast<uint4 *>(stage)[i] = make_uint4(0, 0, 0, 0);
     ptx::fence_proxy_async();
   }
   __syncthreads();
@@ -323,6 +338,24 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
           for (int half = 0; half < 2; ++half) {
             uint4 in[R];
             load_unit(half * bdx + tt, in);
+            if constexpr (ADD) {   // h = bf16(x + res), fp32 add like torch's bf16 add; h goes to sum_out and replaces x below
+              const uint8_t *rsrc = src + (size_t)S * slot_bytes;
+#pragma unroll
+              for (int lr = 0; lr < R; ++lr) {
+                const uint4 rr = *reinterpret_cast<const uint4 *>(rsrc + (size_t)lr * rowstride + (size_t)(half * bdx + tt) * 16);
+                const uint32_t xa[4] = {in[lr].x, in[lr].y, in[lr].z, in[lr].w}, ra[4] = {rr.x, rr.y, rr.z, rr.w};
+                uint32_t ha[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  __nv_bfloat162 h2 = __floats2bfloat162_rn(__fadd_rn(bf16lo_to_f32(xa[k]), bf16lo_to_f32(ra[k])),
+                                                            __fadd_rn(bf16hi_to_f32(xa[k]), bf16hi_to_f32(ra[k])));
+                  ha[k] = *reinterpret_cast<uint32_t *>(&h2);
+                }
+                in[lr] = make_uint4(ha[0], ha[1], ha[2], ha[3]);
+                if (TileMap<R>::row(0, lr) < mrows)
+                  __stcs(reinterpret_cast<uint4 *>(p.sum_out + ((int64_t)r0 + TileMap<R>::row(0, lr)) * KQ) + (half * bdx + tt), in[lr]);
+              }
+            }
             if constexpr (R % 2 == 0) {  // two rows per packed FFMA2, each row's chain in the reference's order
 #pragma unroll
               for (int lr = 0; lr < R; lr += 2) {
@@ -649,14 +682,15 @@ __global__ void __launch_bounds__(THREADS, MINB) quant_tma_kernel(const QuantPar
 
 constexpr int kSmemPerSm = 227 * 1024;
 
-template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN, bool OWN2 = false>
+template <int R, int RT, int FLAVOUR, bool IS_W, bool RMS, bool TAB32, bool OWN, int THREADS, int MINB, bool PS, bool PLAN, bool OWN2 = false,
+          bool ADD = false>
 int launch(const QuantParams &p0, int S, cudaStream_t stream) {
   QuantParams p = p0;
 #ifdef ARCQ_EXPERIMENT
   if (const char *e = getenv("ARCQ_QUANT_DEBUG")) p.debug = atoi(e);
 #endif
-  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB, PS, PLAN, OWN2>;
-  const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S, PLAN, OWN2).total;
+  auto kern = quant_tma_kernel<R, RT, FLAVOUR, IS_W, RMS, TAB32, OWN, THREADS, MINB, PS, PLAN, OWN2, ADD>;
+  const int smem = carve_t(R, p.KQ, p.KE, RMS, TAB32, S, PLAN, OWN2, ADD).total;
   static SmemAttrCache attr_cache = {};  // per instantiation, per device
   if (int rc = ensure_dynamic_smem(kern, smem, attr_cache)) return rc;
   const int sms = sm_count();
@@ -678,6 +712,13 @@ int launch_tab(const QuantParams &p, int S, bool tab32, bool own, cudaStream_t s
       }
       if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB, PS, true>(p, S, st);
       return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB, PS, true>(p, S, st);
+    }
+  }
+  if constexpr (RMS) {
+    if (p.res) {   // fused residual add: unplanned register transposition only (the dispatcher drops the plan)
+      if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB, PS, false, false, true>(p, S, st);
+      if (tab32) return launch<R, RT, FLAVOUR, IS_W, RMS, true, false, THREADS, MINB, PS, false, false, true>(p, S, st);
+      return launch<R, RT, FLAVOUR, IS_W, RMS, false, false, THREADS, MINB, PS, false, false, true>(p, S, st);
     }
   }
   if (own) return launch<R, RT, FLAVOUR, IS_W, RMS, false, true, THREADS, MINB, PS, false>(p, S, st);

@@ -152,7 +152,14 @@ class ArcDecoderLayer(torch.nn.Module):
         q, k, v = (t.reshape(shp).transpose(1, 2) for t in (q, k, v))
         q, k = _rope(q, k)
         a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B * S, -1).contiguous()
-        h = h + self._row(self.o, a).view(B, S, H)              # quantise (local permutation + ARC) -> GEMM -> all-reduce
+        o = self._row(self.o, a)                                # quantise (local permutation + ARC) -> GEMM -> all-reduce
+        if self.fused and 2048 <= H <= 8192 and H % 64 == 0 and self.ke_gu % 64 == 0:
+            # residual add + norm + quantise of the MLP block in ONE launch (modeling_arc.py:294-301): same bits as h + o
+            qx, sfx, hs = ag.add_rmsnorm_quantize_x(o, x2d, self.norm2, self.cfg.eps, self.idx_h2, self.ke_gu)
+            h = hs.view(B, S, H)
+            m = ag.matmul(qx, self.gu_w[0], sfx, self.gu_w[1], self.one, col_scale=self.gu_w[2], epilogue=ag.EPILOGUE_SWIGLU)
+            return h + self._row(self.down, m).view(B, S, H)
+        h = h + o.view(B, S, H)
         x2d = h.reshape(B * S, H)
         if self.fused:
             qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm2, self.cfg.eps, self.idx_h2, self.ke_gu)

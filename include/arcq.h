@@ -128,6 +128,15 @@ int arcq_quantize_x_ex(const void *x, int64_t M, int KQ, const int16_t *idx, int
                        const uint16_t *plan_dev, const float *amax_dev, int prescale_mode, void *qx,
                        void *sfx, float *scale_out, void *stream);
 
+/* The residual add in front of the norm, fused: `hidden_states = residual + hidden_states` followed by
+ * the rmsnorm_quantize_x of the next norm (benchmarks/modeling_arc.py:294-301, model/qLlamaLayer.py:162-166,295-300):
+ *   sum_out bf16 [M, H] = bf16(x + res)   (fp32 add, RNE -- what torch's bf16 add computes; may alias neither input)
+ *   (qx, sfx)           = arcq_rmsnorm_quantize_x(sum_out, w, eps, ...), byte for byte.
+ * One pass: x and res are read once, the sum is written once; the separate torch add (2 reads + 1 write) and the norm's
+ * re-read of its result disappear.  H, KE multiples of 64, 2048 <= H <= 8192, else ARCQ_ENOSUP. */
+int arcq_add_rmsnorm_quantize_x(const void *x, const void *res, const void *w, float eps, int64_t M, int H,
+                                const int16_t *idx, int KE, void *sum_out, void *qx, void *sfx, void *stream);
+
 /* One linear (arcq_quantize_x followed by arcq_gemm_nvfp4: y bf16 [M, N] = alpha * Q(x[:, idx]) . (qw.sfw)^T) for callers
  * that cannot allocate device memory -- code under CUDA-graph capture, tight serving loops, harnesses that forbid
  * cudaMalloc.  NO COUNTERPART IN THE REFERENCE.  The quantised activation
