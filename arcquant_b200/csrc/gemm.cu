@@ -405,9 +405,9 @@ extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa,
   const int sms = sm_count();
   if (sms <= 0) return ARCQ_ECUDA;
   if (swiglu) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, 1, d, ldd, st);
-  // small M: weight-streaming bound; split K over a thread-block cluster so every SM pulls on HBM (gemm_splitk.cu)
+  // small M (<= 1024 rows, few output tiles): split K over a thread-block cluster so every SM pulls on the weight stream (gemm_splitk.cu)
   const int splits = o.gemm_splitk >= 0 ? o.gemm_splitk : splitk_choice((int)M, (int)N, (int)K);
-  if (splits >= 2 && M <= 128)
+  if (splits >= 2 && (M <= 1024 || o.gemm_splitk >= 2))
     return launch_gemm_splitk(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, d, ldd, splits, st);
   // cta_group::2 kernel for shapes with at least one 256 x 256 tile per SM pair
   const int64_t ptiles = ((M + 255) / 256) * ((N + 255) / 256);

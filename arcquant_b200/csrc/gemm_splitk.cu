@@ -1,4 +1,4 @@
-// gemm_splitk.cu -- NVFP4 block-scaled GEMM for SMALL M (<= 128 rows: decode / short prefill chunks).
+// gemm_splitk.cu -- NVFP4 block-scaled GEMM for SMALL M (decode / short prefill chunks: up to 8 row tiles of 128).
 //
 // At M <= 128 the GEMM is a weight stream: 0.5625 * K * N bytes of codes + scales against 2 * M * N * K FLOPs, two
 // to three orders of magnitude under the tensor-core ridge (SURVEY.md §8d "min(tensor, HBM)").  One 128 x 128 output
@@ -64,7 +64,7 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = p.splits;
   const uint32_t rank = ptx::cluster_ctarank();
-  const int nt = blockIdx.x / S;
+  const int nt = blockIdx.x / S, mt = blockIdx.y;   // output tile (mt, nt); the S CTAs of a cluster split its K range
   const int nkb = (p.K + kKB - 1) / kKB, kc_total = p.K / 64;
   const int kb0 = (int)((int64_t)nkb * rank / S), kb1 = (int)((int64_t)nkb * (rank + 1) / S);
 
@@ -96,9 +96,9 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       const uint32_t sf_bytes = (uint32_t)kchunks * 512u;
       if (ptx::elect_one()) {
         ptx::mbar_arrive_expect_tx(&full[s], Cfg::A_BYTES + Cfg::B_BYTES + 2 * sf_bytes);
-        ptx::tma_load_2d(st, &tmap_a, kb * kKBytes, 0, &full[s]);
+        ptx::tma_load_2d(st, &tmap_a, kb * kKBytes, mt * kTM, &full[s]);
         ptx::tma_load_2d(st + Cfg::A_BYTES, &tmap_b, kb * kKBytes, nt * kTN, &full[s]);
-        ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)kb * 4) * 512, sf_bytes, &full[s]);
+        ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES, p.sfa + ((size_t)mt * kc_total + kb * 4) * 512, sf_bytes, &full[s]);
         ptx::bulk_load(st + Cfg::A_BYTES + Cfg::B_BYTES + Cfg::SF_BYTES, p.sfb + ((size_t)nt * kc_total + kb * 4) * 512, sf_bytes,
                        &full[s]);
       }
@@ -137,7 +137,7 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
     const int q = warp & 3;                      // TMEM lane quadrant this warp may read
     ptx::mbar_wait(tfull, 0);                    // every MMA of this CTA is complete: the stage ring is dead, `red` may alias it
     ptx::tc_fence_after();
-    if (q * 32 < p.M) {                          // rows >= M are never reduced
+    if (q * 32 < p.M - mt * kTM) {               // rows >= M are never reduced
       const int row = q * 32 + lane;
 #pragma unroll
       for (int cb = 0; cb < kTN / 32; ++cb) {
@@ -157,7 +157,7 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
   {
     float alpha = p.alpha;
     if (p.alpha_dev) alpha = __ldg(p.alpha_dev);
-    const int Mv = p.M < kTM ? p.M : kTM;
+    const int Mv = p.M - mt * kTM < kTM ? p.M - mt * kTM : kTM;
     const int nunits = Mv * (kTN / 32);          // a unit = 32 consecutive columns of one row, one per warp step
     constexpr int NW = kSkThreads / 32;
     const uint32_t red_s = ptx::smem_u32(red);
@@ -174,7 +174,7 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       if (gcol < p.N) {
         float sc = alpha;
         if (p.col_scale) sc = __fmul_rn(alpha, __ldg(p.col_scale + gcol));
-        p.d[(size_t)row * p.ldd + gcol] = __float2bfloat16_rn(sc * acc);
+        p.d[(size_t)(mt * kTM + row) * p.ldd + gcol] = __float2bfloat16_rn(sc * acc);
       }
     }
   }
@@ -187,19 +187,22 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
 
 }  // namespace
 
+// Measured on the Llama-3-8B shapes (profiles/r2_midm_splitk_ab.log): the cluster kernel wins while the output has few
+// 128 x 128 tiles -- up to 32 tiles with 8 splits (q/o and k/v at M <= 128 .. 512: 10.0 vs 12.1 us, 7.8 vs 11.6 us; down at
+// M <= 128: 13.7 vs 29.6 us), up to 64 tiles with 4 splits when K is long (down at M = 256: 22.2 vs 30.5 us) -- and loses
+// beyond that (its TMEM -> shared -> DSMEM reduction costs more than the idle SMs were worth), so: no split otherwise.
 int splitk_choice(int M, int N, int K) {
-  if (M > kTM) return 0;
-  const int sms = sm_count();
-  if (sms <= 0) return 0;
-  const int tiles = (N + kTN - 1) / kTN, nkb = (K + kKB - 1) / kKB;
+  if (M > 8 * kTM) return 0;
+  const int tiles = ((N + kTN - 1) / kTN) * ((M + kTM - 1) / kTM), nkb = (K + kKB - 1) / kKB;
+  const int max_s = tiles <= 32 ? 8 : (tiles <= 64 && nkb >= 32 ? 4 : 1);
   int S = 1;
-  while (S * 2 <= 8 && tiles * S * 2 <= 2 * sms && nkb / (S * 2) >= 2) S *= 2;
+  while (S * 2 <= max_s && nkb / (S * 2) >= 2) S *= 2;
   return S >= 2 ? S : 0;
 }
 
 int launch_gemm_splitk(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
                        const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, int splits, cudaStream_t stream) {
-  if (M > kTM) { set_error("split-K kernel takes M <= 128, got %d", M); return ARCQ_ENOSUP; }
+  if (M > 65535 * kTM) { set_error("split-K kernel: M=%d too large", M); return ARCQ_ENOSUP; }
   const int nkb = (K + kKB - 1) / kKB;
   if (splits > 8) splits = 8;
   while (splits > 1 && (nkb < splits || (splits & (splits - 1)))) --splits;   // power of two, every CTA gets a k-block
@@ -217,7 +220,7 @@ int launch_gemm_splitk(const void *a, const void *b, const void *sfa, const void
   attr[0].val.clusterDim.x = splits;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
-  cfg.gridDim = dim3(((N + kTN - 1) / kTN) * splits);
+  cfg.gridDim = dim3(((N + kTN - 1) / kTN) * splits, (M + kTM - 1) / kTM);
   cfg.blockDim = dim3(kSkThreads);
   cfg.dynamicSmemBytes = SkCfg::SMEM_BYTES;
   cfg.stream = stream;

@@ -77,6 +77,22 @@ def test_splitk_small_m(arcq_option, splits, M, N, K):
     assert worst <= 1.0 and rel < 2e-3, "splitk=%d M=%d N=%d K=%d: max err/tol %.3g rel-F %.3g" % (splits, M, N, K, worst, rel)
 
 
+@pytest.mark.parametrize("splits", [2, 4, -1])
+@pytest.mark.parametrize("M,N,K", [(200, 4096, 4352), (256, 4096, 14848), (520, 1024, 4352), (1024, 512, 2176), (300, 6144 + 8, 4160)])
+def test_splitk_several_row_tiles(arcq_option, splits, M, N, K):
+    """The same kernel over several 128-row tiles (grid.y): 128 < M <= 1024 with few output tiles, where one CTA per tile
+    leaves most SMs without work (down_proj at M = 256: 32 CTAs x 58 k-blocks)."""
+    from arcquant_b200 import agemm
+    if splits >= 0:
+        arcq_option("gemm_splitk", splits)
+    qa, sfa = _rand_operand(M, K, 7)
+    qb, sfb = _rand_operand(N, K, 8)
+    y = agemm.matmul(qa, qb, sfa, sfb, 1e-3)
+    torch.cuda.synchronize()
+    worst, rel = T.check_gemm(y, qa, sfa, qb, sfb, 1e-3, torch.arange(M))
+    assert worst <= 1.0 and rel < 2e-3, "splitk=%d M=%d N=%d K=%d: max err/tol %.3g rel-F %.3g" % (splits, M, N, K, worst, rel)
+
+
 @pytest.mark.parametrize("M", [64, 520, 8192])
 def test_fused_qkv_equals_separate_launches(M):
     """q/k/v (qLlamaLayer.py:301-303) as ONE launch over the concatenated weight with per-column scales: every column
