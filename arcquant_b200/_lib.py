@@ -25,6 +25,7 @@ SIGNATURES = {
     "arcq_add_rmsnorm_quantize_x": (_I32, [_VP, _VP, _VP, _F32, _I64, _I32, _VP, _I32, _VP, _VP, _VP, _VP]),
     "arcq_gemm_nvfp4": (_I32, [_VP, _VP, _VP, _VP, _I64, _I64, _I64, _F32, _VP, _VP, _VP]),
     "arcq_gemm_nvfp4_ex": (_I32, [_VP, _VP, _VP, _VP, _I64, _I64, _I64, _F32, _VP, _VP, _I32, _VP, _I64, _VP]),
+    "arcq_gemm_nvfp4_ex2": (_I32, [_VP, _VP, _VP, _VP, _I64, _I64, _I64, _F32, _VP, _VP, _VP, _I32, _VP, _I64, _VP]),
     "arcq_absmax": (_I32, [_VP, _I64, _VP, _VP]),
     "arcq_quantize_x_scaled": (_I32, [_VP, _I64, _I32, _VP, _I32, _I32, _VP, _I32, _VP, _VP, _VP, _VP]),
     "arcq_set_option": (_I32, [ctypes.c_char_p, ctypes.c_char_p]),

@@ -177,7 +177,7 @@ def _c_add_rmsnorm_quantize_x(X, residual, W, eps, reorder_index, KE):
     return q, sf, s
 
 
-def _c_matmul(A, B, SFA, SFB, scale, col_scale=None, epilogue: int = 0, out=None):
+def _c_matmul(A, B, SFA, SFB, scale, col_scale=None, epilogue: int = 0, out=None, bias=None):
     """nvfp4 matmul, return bfloat16 tensor (bindings.cpp:99-120): scale * (A.SFA) @ (B.SFB)^T."""
     L = _lib.load()
     _need(A, "A", torch.uint8, 2)
@@ -208,6 +208,12 @@ def _c_matmul(A, B, SFA, SFB, scale, col_scale=None, epilogue: int = 0, out=None
         if col_scale.numel() != N or col_scale.device != A.device:
             raise RuntimeError("col_scale must hold %d float32 on %s" % (N, A.device))
         cs = col_scale.data_ptr()
+    bp = 0
+    if bias is not None:  # y + self.bias of the reference's linear (qLinearLayer.py:74-75), in the epilogue
+        _need(bias, "bias", torch.bfloat16, 1)
+        if bias.numel() != N or bias.device != A.device or epilogue != EPILOGUE_NONE:
+            raise RuntimeError("bias must hold %d bfloat16 on %s and needs epilogue == EPILOGUE_NONE" % (N, A.device))
+        bp = bias.data_ptr()
     out_cols = N // 2 if epilogue == EPILOGUE_SWIGLU else N
     with torch.cuda.device(A.device):
         if out is None:
@@ -219,8 +225,8 @@ def _c_matmul(A, B, SFA, SFB, scale, col_scale=None, epilogue: int = 0, out=None
             if tuple(out.shape) != (M, out_cols) or out.stride(1) != 1 or out.stride(0) < out_cols:
                 raise RuntimeError("out must be [%d, %d] with unit column stride, got %s strides %s"
                                    % (M, out_cols, tuple(out.shape), out.stride()))
-        rc = L.arcq_gemm_nvfp4_ex(A.data_ptr(), B.data_ptr(), SFA.data_ptr(), SFB.data_ptr(), M, N, K, alpha,
-                                  alpha_dev, cs, int(epilogue), out.data_ptr(), out.stride(0), _stream(A))
+        rc = L.arcq_gemm_nvfp4_ex2(A.data_ptr(), B.data_ptr(), SFA.data_ptr(), SFB.data_ptr(), M, N, K, alpha,
+                                   alpha_dev, cs, bp, int(epilogue), out.data_ptr(), out.stride(0), _stream(A))
     _lib.check(rc, "arcq_gemm_nvfp4")
     return out
 

@@ -175,7 +175,8 @@ std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> reorder_quantize_x_scale
 }
 
 torch::Tensor matmul(const torch::Tensor &A, const torch::Tensor &B, const torch::Tensor &SFA, const torch::Tensor &SFB, const py::object &scale,
-                     const c10::optional<torch::Tensor> &col_scale, int epilogue, const c10::optional<torch::Tensor> &out) {
+                     const c10::optional<torch::Tensor> &col_scale, int epilogue, const c10::optional<torch::Tensor> &out,
+                     const c10::optional<torch::Tensor> &bias) {
   need(A, "A", torch::kUInt8, 2);
   need(B, "B", torch::kUInt8, 2);
   need(SFA, "SFA", torch::kUInt8);
@@ -203,6 +204,13 @@ torch::Tensor matmul(const torch::Tensor &A, const torch::Tensor &B, const torch
     TORCH_CHECK(col_scale->numel() == N && col_scale->device() == A.device(), "col_scale must hold ", N, " float32 on ", A.device());
     cs = col_scale->data_ptr<float>();
   }
+  const void *bias_ptr = nullptr;
+  if (bias.has_value()) {   // y + self.bias of the reference's linear (qLinearLayer.py:74-75), in the epilogue
+    need(*bias, "bias", torch::kBFloat16, 1);
+    TORCH_CHECK(bias->numel() == N && bias->device() == A.device() && epilogue == ARCQ_EPILOGUE_NONE,
+                "bias must hold ", N, " bfloat16 on ", A.device(), " and needs epilogue == EPILOGUE_NONE");
+    bias_ptr = bias->data_ptr();
+  }
   const int64_t out_cols = epilogue == ARCQ_EPILOGUE_SWIGLU ? N / 2 : N;
   const c10::cuda::CUDAGuard guard(A.device());
   torch::Tensor C;
@@ -216,8 +224,8 @@ torch::Tensor matmul(const torch::Tensor &A, const torch::Tensor &B, const torch
   } else {
     C = torch::empty({M, out_cols}, torch::dtype(torch::kBFloat16).device(A.device()));
   }
-  fail(arcq_gemm_nvfp4_ex(A.data_ptr(), B.data_ptr(), SFA.data_ptr(), SFB.data_ptr(), M, N, K, alpha, alpha_dev, cs, epilogue, C.data_ptr(), ldd,
-                          stream_of(A)),
+  fail(arcq_gemm_nvfp4_ex2(A.data_ptr(), B.data_ptr(), SFA.data_ptr(), SFB.data_ptr(), M, N, K, alpha, alpha_dev, cs, bias_ptr, epilogue, C.data_ptr(),
+                           ldd, stream_of(A)),
        "arcq_gemm_nvfp4");
   return C;
 }
@@ -235,7 +243,7 @@ void set_option(const std::string &name, const std::string &value) { fail(arcq_s
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.doc() = "B200-native agemm: NVFP4 + ARC quantise and block-scaled GEMM (drop-in for kernels/src/bindings.cpp)";
   m.def("matmul", &matmul, "nvfp4 matmul, return bfloat16 tensor", py::arg("A"), py::arg("B"), py::arg("SFA"), py::arg("SFB"), py::arg("scale"),
-        py::arg("col_scale") = py::none(), py::arg("epilogue") = 0, py::arg("out") = py::none());
+        py::arg("col_scale") = py::none(), py::arg("epilogue") = 0, py::arg("out") = py::none(), py::arg("bias") = py::none());
   m.def("reorder_quantize_x", &reorder_quantize_x, "Reorder and quantize activation, return K + KE channels", py::arg("X"),
         py::arg("reorder_index"), py::arg("KE"), py::arg("flavour") = -1);
   m.def("reorder_quantize_w", &reorder_quantize_w, "Reorder and quantize weight, return K + KE channels", py::arg("W"),

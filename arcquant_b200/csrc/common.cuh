@@ -107,6 +107,21 @@ __device__ __forceinline__ float e2m1_to_f32(uint32_t c) {
   return __uint_as_float(bits);
 }
 
+// per-column bias in the GEMM epilogues: bf16(float(y) + float(bias)) on two packed bf16 -- torch's `y + self.bias` on bf16
+// tensors (model/qLinearLayer.py:74-75), applied to the ALREADY ROUNDED output so the fused result has the same bits
+__device__ __forceinline__ uint32_t bias_add_bf16x2(uint32_t y, uint32_t b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(__fadd_rn(bf16lo_to_f32(y), bf16lo_to_f32(b)), __fadd_rn(bf16hi_to_f32(y), bf16hi_to_f32(b)));
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+// the eight bias values of output columns [gcol, gcol + 8) (zeros past ncols); gcol % 8 == 0 and a 16-byte aligned vector
+__device__ __forceinline__ uint4 load_bias8(const __nv_bfloat16 *bias, int gcol, int ncols) {
+  if (gcol + 8 <= ncols) return __ldg(reinterpret_cast<const uint4 *>(bias + gcol));
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
+  for (int e = 0; e < 8; ++e)
+    if (gcol + e < ncols) w[e >> 1] |= (uint32_t)__bfloat16_as_ushort(bias[gcol + e]) << (16 * (e & 1));
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 __device__ __forceinline__ uint32_t f32_to_bf16_bits(float f) {
   return (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(f));
 }

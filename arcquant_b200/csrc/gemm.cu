@@ -61,7 +61,7 @@ struct GemmParams {
   float alpha;
   int M, N, K;
   int64_t ldd;             // row stride of d in elements
-  int tiles_m, tiles_n;
+  int tiles_m, tiles_n;  const __nv_bfloat16 *col_bias;  // nullable bf16 [N]: added to the rounded output like torch's `y + bias` (qLinearLayer.py:74-75)
 };
 
 template <int BN, int STAGES, int PC>
@@ -239,10 +239,13 @@ gemm_nvfp4_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         __syncwarp();
         const int j = lane & (CH - 1);
         const int gcol = nt * BN + half * HC + pass * PC + j * 8;
+        uint4 bv = make_uint4(0u, 0u, 0u, 0u);
+        if (p.col_bias && gcol < p.N) bv = load_bias8(p.col_bias, gcol, p.N);
 #pragma unroll
         for (int i = 0; i < CH; ++i) {  // 32 / CH rows per instruction, CH instructions
           const int rr = i * (32 / CH) + lane / CH;
-          const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
+          uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
+          if (p.col_bias) v = make_uint4(bias_add_bf16x2(v.x, bv.x), bias_add_bf16x2(v.y, bv.y), bias_add_bf16x2(v.z, bv.z), bias_add_bf16x2(v.w, bv.w));
           const int grow = mt * kBM + q * 32 + rr;
           if (grow < p.M && gcol < p.N) {
             __nv_bfloat16 *dst = p.d + (size_t)grow * p.ldd + gcol;
@@ -377,15 +380,17 @@ using namespace arcq;
 
 namespace arcq {
 int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                     const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream);
+                     const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream,
+                     const void *col_bias = nullptr);
 int launch_gemm_splitk(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                       const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, int splits, cudaStream_t stream);
+                       const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, int splits, cudaStream_t stream,
+                       const void *col_bias = nullptr);
 int splitk_choice(int M, int N, int K);  // 0 = do not split
 }
 
-extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
-                                  int64_t K, float alpha, const float *alpha_dev, const float *col_scale_dev, int epilogue,
-                                  void *d, int64_t ldd, void *stream) {
+extern "C" int arcq_gemm_nvfp4_ex2(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
+                                   int64_t K, float alpha, const float *alpha_dev, const float *col_scale_dev,
+                                   const void *col_bias_dev, int epilogue, void *d, int64_t ldd, void *stream) {
   if (!a || !b || !sfa || !sfb || !d) { set_error("null pointer argument"); return ARCQ_EINVAL; }
   if (M < 0 || N < 0 || M > 0x7fffff00 || N > 0x7fffff00) { set_error("M/N out of range"); return ARCQ_EINVAL; }
   if (K <= 0 || K % 64 || K > (1 << 20)) { set_error("K=%lld must be a positive multiple of 64", (long long)K); return ARCQ_EINVAL; }
@@ -395,6 +400,10 @@ extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa,
   }
   if (epilogue != ARCQ_EPILOGUE_NONE && epilogue != ARCQ_EPILOGUE_SWIGLU) { set_error("unknown epilogue %d", epilogue); return ARCQ_EINVAL; }
   const bool swiglu = epilogue == ARCQ_EPILOGUE_SWIGLU;
+  if (col_bias_dev && (swiglu || ((uintptr_t)col_bias_dev & 15))) {
+    set_error("col_bias_dev must be 16-byte aligned and cannot be combined with the SwiGLU epilogue");
+    return ARCQ_EINVAL;
+  }
   if (swiglu && N % 256) { set_error("the SwiGLU epilogue needs N %% 256 == 0 (128-row gate/up interleave), got N=%lld", (long long)N); return ARCQ_EINVAL; }
   const int64_t out_cols = swiglu ? N / 2 : N;
   if (ldd == 0) ldd = out_cols;
@@ -408,13 +417,13 @@ extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa,
   // small M (<= 1024 rows, few output tiles): split K over a thread-block cluster so every SM pulls on the weight stream (gemm_splitk.cu)
   const int splits = o.gemm_splitk >= 0 ? o.gemm_splitk : splitk_choice((int)M, (int)N, (int)K);
   if (splits >= 2 && (M <= 1024 || o.gemm_splitk >= 2))
-    return launch_gemm_splitk(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, d, ldd, splits, st);
+    return launch_gemm_splitk(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, d, ldd, splits, st, col_bias_dev);
   // cta_group::2 kernel for shapes with at least one 256 x 256 tile per SM pair
   const int64_t ptiles = ((M + 255) / 256) * ((N + 255) / 256);
   const bool use_pair = o.gemm_pair >= 0 ? o.gemm_pair != 0 : ptiles >= sms / 2;
-  if (use_pair) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, 0, d, ldd, st);
+  if (use_pair) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, 0, d, ldd, st, col_bias_dev);
   GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, col_scale_dev, alpha,
-               (int)M, (int)N, (int)K, ldd, 0, 0};
+               (int)M, (int)N, (int)K, ldd, 0, 0, (const __nv_bfloat16 *)col_bias_dev};
   const int64_t tiles256 = ((M + kBM - 1) / kBM) * ((N + 255) / 256);
   int bn = o.gemm_bn;
   if (bn != 128 && bn != 256) {
@@ -423,6 +432,12 @@ extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa,
   }
   if (bn == 256) return launch_gemm<256, 4, 16>(a, b, p, st);
   return launch_gemm<128, 5, 64>(a, b, p, st);
+}
+
+extern "C" int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,
+                                  int64_t K, float alpha, const float *alpha_dev, const float *col_scale_dev, int epilogue,
+                                  void *d, int64_t ldd, void *stream) {
+  return arcq_gemm_nvfp4_ex2(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale_dev, nullptr, epilogue, d, ldd, stream);
 }
 
 extern "C" int arcq_gemm_nvfp4(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M, int64_t N,

@@ -69,6 +69,7 @@ struct PParams {
   // receive buffer of its owner o = g / rs_rows, slot rs_rank: peer_d[o] + ((rs_rank * rs_rows) + g - o * rs_rows) * ldd
   __nv_bfloat16 *peer_d[ARCQ_MAX_PEERS];
   int rs_rows, rs_rank;
+  const __nv_bfloat16 *col_bias;   // nullable bf16 [N] (plain epilogue only): torch's `y + bias` on the rounded output
 };
 
 // bf16(silu(g)) * u exactly as torch computes `F.silu(g) * u` on bf16 tensors: silu in fp32 (x / (1 + exp(-x)), IEEE
@@ -348,10 +349,17 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         __syncwarp();
         const int j = lane & (CH - 1);
         const int gcol = out_col0 + pass * kPC + j * 8;
+        uint4 bv = make_uint4(0u, 0u, 0u, 0u);
+        if constexpr (!SWIGLU) {
+          if (p.col_bias && gcol < ncols_out) bv = load_bias8(p.col_bias, gcol, ncols_out);
+        }
 #pragma unroll
         for (int i = 0; i < CH; ++i) {
           const int rr = i * (32 / CH) + lane / CH;
-          const uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
+          uint4 v = *reinterpret_cast<const uint4 *>(wst + rr * RB + ((j ^ (rr & (CH - 1))) << 4));
+          if constexpr (!SWIGLU) {
+            if (p.col_bias) v = make_uint4(bias_add_bf16x2(v.x, bv.x), bias_add_bf16x2(v.y, bv.y), bias_add_bf16x2(v.z, bv.z), bias_add_bf16x2(v.w, bv.w));
+          }
           const int grow = row_base + rr;
           if (grow < p.M && gcol < ncols_out) {
             __nv_bfloat16 *dst = dbase + (int64_t)grow * p.ldd + gcol;
@@ -384,7 +392,7 @@ struct ScatterArgs { void *const *peer_recv; int world, rank, rows_per_rank; };
 template <bool SWIGLU>
 static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
                               const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, cudaStream_t stream,
-                              const ScatterArgs *sc = nullptr) {
+                              const ScatterArgs *sc = nullptr, const void *col_bias = nullptr) {
   constexpr int STAGES = SWIGLU ? 4 : 5;   // the silu table takes the fifth stage's place
   using Cfg = PCfg<STAGES, SWIGLU>;
   auto kern = gemm_nvfp4_pair_kernel<STAGES, SWIGLU>;
@@ -413,7 +421,7 @@ static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, con
     if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
     max_pairs[dev] = n;
   }
-  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0};
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0, (const __nv_bfloat16 *)col_bias};
   if (sc) {
     for (int i = 0; i < ARCQ_MAX_PEERS; ++i) p.peer_d[i] = (__nv_bfloat16 *)sc->peer_recv[i < sc->world ? i : sc->world - 1];
     p.rs_rows = sc->rows_per_rank;
@@ -451,9 +459,10 @@ static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, con
 }
 
 int launch_gemm_pair(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                     const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream) {
+                     const float *alpha_dev, const float *col_scale, int swiglu, void *d, int64_t ldd, cudaStream_t stream,
+                     const void *col_bias) {
   if (swiglu) return launch_gemm_pair_t<true>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream);
-  return launch_gemm_pair_t<false>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream);
+  return launch_gemm_pair_t<false>(a, b, sfa, sfb, M, N, K, alpha, alpha_dev, col_scale, d, ldd, stream, nullptr, col_bias);
 }
 
 // row-parallel GEMM whose epilogue IS the first half of the reduce-scatter (always the cta_group::2 kernel: any shape works)

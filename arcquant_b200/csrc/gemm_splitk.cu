@@ -41,6 +41,7 @@ struct SkParams {
   int M, N, K;
   int64_t ldd;
   int splits;
+  const __nv_bfloat16 *col_bias;   // nullable bf16 [N]
 };
 
 __device__ __forceinline__ float ld_dsmem_f32(uint32_t cluster_addr) {
@@ -174,7 +175,9 @@ gemm_nvfp4_splitk_kernel(const __grid_constant__ CUtensorMap tmap_a, const __gri
       if (gcol < p.N) {
         float sc = alpha;
         if (p.col_scale) sc = __fmul_rn(alpha, __ldg(p.col_scale + gcol));
-        p.d[(size_t)(mt * kTM + row) * p.ldd + gcol] = __float2bfloat16_rn(sc * acc);
+        __nv_bfloat16 y = __float2bfloat16_rn(sc * acc);
+        if (p.col_bias) y = __float2bfloat16_rn(__fadd_rn(__bfloat162float(y), __bfloat162float(p.col_bias[gcol])));   // torch's `y + bias`
+        p.d[(size_t)(mt * kTM + row) * p.ldd + gcol] = y;
       }
     }
   }
@@ -201,7 +204,8 @@ int splitk_choice(int M, int N, int K) {
 }
 
 int launch_gemm_splitk(const void *a, const void *b, const void *sfa, const void *sfb, int M, int N, int K, float alpha,
-                       const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, int splits, cudaStream_t stream) {
+                       const float *alpha_dev, const float *col_scale, void *d, int64_t ldd, int splits, cudaStream_t stream,
+                       const void *col_bias) {
   if (M > 65535 * kTM) { set_error("split-K kernel: M=%d too large", M); return ARCQ_ENOSUP; }
   const int nkb = (K + kKB - 1) / kKB;
   if (splits > 8) splits = 8;
@@ -213,7 +217,7 @@ int launch_gemm_splitk(const void *a, const void *b, const void *sfa, const void
   CUtensorMap ta, tb;
   if (int rc = cached_operand_map(&ta, a, M, K / 2, kTM)) return rc;
   if (int rc = cached_operand_map(&tb, b, N, K / 2, kTN)) return rc;
-  SkParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, splits};
+  SkParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, splits, (const __nv_bfloat16 *)col_bias};
   cudaLaunchConfig_t cfg = {};
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;

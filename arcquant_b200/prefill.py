@@ -142,9 +142,7 @@ class ArcDecoderLayer(torch.nn.Module):
         x2d = h.reshape(B * S, H)
         if self.fused:
             qx, sfx = ag.rmsnorm_quantize_x(x2d, self.norm1, self.cfg.eps, self.idx_h1, self.ke_qkv)
-            qkv = ag.matmul(qx, self.qkv_w[0], sfx, self.qkv_w[1], self.one, col_scale=self.qkv_w[2])
-            if self.qkv_bias is not None:
-                qkv = qkv + self.qkv_bias
+            qkv = ag.matmul(qx, self.qkv_w[0], sfx, self.qkv_w[1], self.one, col_scale=self.qkv_w[2], bias=self.qkv_bias)
             q, k, v = qkv.split(H // self.world, dim=1)
         else:
             q, k, v = self._norm_linears(x2d, self.norm1, self.idx_h1, self.ke_qkv, (self.q, self.k, self.v))

@@ -97,9 +97,13 @@ class QLinearShard(torch.nn.Module):
 
     @torch.no_grad()
     def forward_quantized(self, qx, scale_x, scale, out=None):
+        b = self.bias
+        if b is not None and b.dtype == torch.bfloat16 and b.is_contiguous() and b.data_ptr() % 16 == 0:
+            # `y + self.bias` (qLinearLayer.py:74-75) in the GEMM epilogue: same bits, no extra pass over [M, N]
+            return self.agemm.matmul(qx, self.W, scale_x, self.scale_w, scale * self.scale, out=out, bias=b)
         y = self.agemm.matmul(qx, self.W, scale_x, self.scale_w, scale * self.scale, out=out)
-        if self.bias is not None:
-            y = y + self.bias
+        if b is not None:
+            y = y + b
         return y
 
     @torch.no_grad()

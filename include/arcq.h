@@ -91,6 +91,15 @@ int arcq_gemm_nvfp4_ex(const void *a, const void *b, const void *sfa, const void
                        int64_t N, int64_t K, float alpha, const float *alpha_dev,
                        const float *col_scale_dev, int epilogue, void *d, int64_t ldd, void *stream);
 
+/* arcq_gemm_nvfp4_ex plus a per-column bias: col_bias_dev (nullable) bf16 [N], 16-byte aligned; the epilogue computes
+ * bf16(float(y) + float(bias[n])) on the ALREADY ROUNDED bf16 output y -- exactly torch's `y = y + self.bias` of the
+ * reference's linear layer (model/qLinearLayer.py:74-75; Qwen's q/k/v projections) without its extra pass over [M, N].
+ * Not combinable with ARCQ_EPILOGUE_SWIGLU. */
+int arcq_gemm_nvfp4_ex2(const void *a, const void *b, const void *sfa, const void *sfb, int64_t M,
+                        int64_t N, int64_t K, float alpha, const float *alpha_dev,
+                        const float *col_scale_dev, const void *col_bias_dev, int epilogue, void *d,
+                        int64_t ldd, void *stream);
+
 /* Fused per-tensor pre-scale of the reference callers (NVFP4_reorder_quantize_x, model/qLlamaLayer.py:73-77,
  * qQwenLayer.py:72-75, benchmarks/modeling_arc.py:58-61: `scale = max|x| / 2688; agemm.reorder_quantize_x(x / scale)`).
  *   arcq_absmax: amax_out[0] = max |x| over n bf16 elements, as fp32 (one memset + one kernel, stream ordered);

@@ -187,3 +187,26 @@ def test_out_slice_with_row_stride():
         agemm.matmul(qa, qb, sfa, sfb, 1e-3, out=torch.empty((M, N + 8), dtype=torch.bfloat16, device="cuda"))
     with pytest.raises(RuntimeError):
         agemm.matmul(qa, qb, sfa, sfb, 1e-3, out=torch.empty((M, N), dtype=torch.float16, device="cuda"))
+
+
+@pytest.mark.parametrize("variant,M,N,K", [("default", 4096, 10752, 3840), ("default", 300, 1000, 2176), ("pair", 520, 768 + 8, 1088),
+                                           ("bn128", 200, 384, 576), ("bn256", 700, 512, 4352), ("splitk", 64, 4096, 4352),
+                                           ("splitk", 256, 1024, 4352)])
+def test_bias_epilogue_equals_torch_add(arcq_option, variant, M, N, K):
+    """matmul(..., bias=b) == matmul(...) + b, bit for bit, in every kernel family (the reference's linear adds the bias in
+    torch after the GEMM, /root/reference/model/qLinearLayer.py:74-75): the epilogue adds it to the already rounded output."""
+    from arcquant_b200 import agemm
+    for name, val in {"default": {}, "pair": {"gemm_pair": 1, "gemm_splitk": 0}, "bn128": {"gemm_pair": 0, "gemm_bn": 128, "gemm_splitk": 0},
+                      "bn256": {"gemm_pair": 0, "gemm_bn": 256, "gemm_splitk": 0}, "splitk": {"gemm_splitk": 4}}[variant].items():
+        arcq_option(name, val)
+    qa, sfa = _rand_operand(M, K, 9)
+    qb, sfb = _rand_operand(N, K, 10)
+    g = torch.Generator(device="cuda").manual_seed(N)
+    bias = (torch.randn(N, device="cuda", generator=g) * 3).to(torch.bfloat16)
+    cs = (torch.rand(N, device="cuda", generator=g) + 0.5).float()
+    y0 = agemm.matmul(qa, qb, sfa, sfb, 1e-3, col_scale=cs)
+    y1 = agemm.matmul(qa, qb, sfa, sfb, 1e-3, col_scale=cs, bias=bias)
+    torch.cuda.synchronize()
+    assert torch.equal(y1, y0 + bias), "%s M=%d N=%d K=%d" % (variant, M, N, K)
+    with pytest.raises(RuntimeError):
+        agemm.matmul(qa, qb, sfa, sfb, 1e-3, bias=bias[:-8].contiguous())
