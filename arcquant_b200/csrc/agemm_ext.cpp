@@ -189,12 +189,15 @@ torch::Tensor matmul(const torch::Tensor &A, const torch::Tensor &B, const torch
   float alpha = 0.0f;
   const float *alpha_dev = nullptr;
   torch::Tensor scale_t;
-  if (py::isinstance<torch::Tensor>(scale) && (scale_t = scale.cast<torch::Tensor>()).is_cuda() &&
-      scale_t.scalar_type() == torch::kFloat32 && scale_t.numel() == 1 && scale_t.device() == A.device()) {
+  // THPVariable_Check, not py::isinstance<torch::Tensor>: at::Tensor is not a pybind11-registered class, so the latter is
+  // always false and a tensor `scale` would silently go through __float__ (.item(): a host sync, and an error under capture)
+  const bool scale_is_tensor = THPVariable_Check(scale.ptr());
+  if (scale_is_tensor) scale_t = scale.cast<torch::Tensor>();
+  if (scale_is_tensor && scale_t.is_cuda() && scale_t.scalar_type() == torch::kFloat32 && scale_t.numel() == 1 && scale_t.device() == A.device()) {
     alpha_dev = scale_t.data_ptr<float>();  // read by the kernel: no host sync
-  } else if (py::isinstance<torch::Tensor>(scale)) {
-    TORCH_CHECK(scale_t.defined() ? scale_t.numel() == 1 : scale.cast<torch::Tensor>().numel() == 1, "`scale` must hold one value");
-    alpha = (scale_t.defined() ? scale_t : scale.cast<torch::Tensor>()).item<float>();  // any other tensor: .item(), a D2H sync like the reference's `const float scale` (:104)
+  } else if (scale_is_tensor) {
+    TORCH_CHECK(scale_t.numel() == 1, "`scale` must hold one value");
+    alpha = scale_t.item<float>();  // any other tensor: .item(), a D2H sync like the reference's `const float scale` (:104)
   } else {
     alpha = scale.cast<float>();
   }

@@ -173,6 +173,69 @@ class ArcDecoderLayer(torch.nn.Module):
             dist.all_reduce(y, op=dist.ReduceOp.SUM, group=self.group)
         return y
 
+    # ---- sequence-parallel form over peer memory (SeqParallelExchange below) ----
+    @torch.no_grad()
+    def forward_sp(self, xc: "SeqParallelExchange", h_loc, pending, B, S):
+        """This rank owns tokens [rank * M / W, +M / W) of the residual stream (h_loc [M/W, H]); `pending` is the previous
+        layer's reduce-scattered down_proj output, not yet added.  Per layer: 2 x (norm + quantise of the own tokens ->
+        gather of codes + scale blocks by peer stores -> column-parallel GEMM) and 2 x (row-parallel GEMM whose epilogue
+        scatters into the owners' slots -> barrier + slot sum); both residual adds ride in front of the norms
+        (add_rmsnorm_quantize_x).  No NCCL call, no torch pass over the residual stream.  Returns (h_loc, pending)."""
+        ag, H, W, eps = self.agemm, self.cfg.hidden, self.world, self.cfg.eps
+        M = B * S
+        if pending is None:
+            qx, sfx = ag.rmsnorm_quantize_x(h_loc, self.norm1, eps, self.idx_h1, self.ke_qkv)
+        else:
+            qx, sfx, h_loc = ag.add_rmsnorm_quantize_x(pending, h_loc, self.norm1, eps, self.idx_h1, self.ke_qkv)
+        qf, sff = xc.gather(qx, sfx, H + self.ke_qkv)
+        qkv = ag.matmul(qf, self.qkv_w[0], sff, self.qkv_w[1], self.one, col_scale=self.qkv_w[2], bias=self.qkv_bias)
+        q, k, v = qkv.split(H // W, dim=1)
+        shp = (B, S, self.local_heads, self.head_dim)
+        q, k, v = (t.reshape(shp).transpose(1, 2) for t in (q, k, v))
+        q, k = _rope(q, k)
+        a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(M, -1).contiguous()
+        o_loc = xc.row_linear(self.o, a)
+        qx, sfx, h_loc = ag.add_rmsnorm_quantize_x(o_loc, h_loc, self.norm2, eps, self.idx_h2, self.ke_gu)
+        qf, sff = xc.gather(qx, sfx, H + self.ke_gu)
+        m = ag.matmul(qf, self.gu_w[0], sff, self.gu_w[1], self.one, col_scale=self.gu_w[2], epilogue=ag.EPILOGUE_SWIGLU)
+        return h_loc, xc.row_linear(self.down, m)
+
+
+class SeqParallelExchange:
+    """Peer-memory buffers of the sequence-parallel prefill (one set per model: every layer has the same shapes) and the
+    two exchange steps on them (arcquant_b200/peer.py).  Reuse is safe without double buffering because the calls strictly
+    alternate: a peer reaches its next store into a buffer only after a barrier this rank entered after its last read."""
+
+    def __init__(self, cfg: PrefillConfig, dev, tokens: int, ke_max: int, agemm):
+        from . import peer as P
+        self.P, self.agemm = P, agemm
+        self.group = P.PeerGroup(dist, dev).init_flags()
+        W = self.group.world
+        if tokens % (128 * W):
+            raise ValueError("sequence-parallel prefill needs tokens %% (128 * world) == 0")
+        self.M, self.Mloc, self.H = tokens, tokens // W, cfg.hidden
+        K = cfg.hidden + ke_max
+        self.qbuf = P.PeerBuffer(self.group, tokens * K // 2)
+        self.sbuf = P.PeerBuffer(self.group, agemm.sf_bytes(tokens, K))
+        self.recv = P.PeerBuffer(self.group, P.world_bytes(W, self.Mloc, cfg.hidden))
+        self.out = [torch.empty((self.Mloc, cfg.hidden), dtype=torch.bfloat16, device=dev) for _ in range(2)]
+        self.flip = 0
+
+    def gather(self, qx, sfx, K):
+        """codes [M/W, K/2] + scale blocks of the own tokens -> every rank's [M, K/2] / swizzled scale buffer"""
+        g, r = self.group, self.group.rank
+        nsf = self.Mloc * K // 16
+        g.allgather(qx, self.qbuf, r * qx.numel(), sfx[:nsf], self.sbuf, r * nsf, channel=1)
+        return self.qbuf.view(torch.uint8, (self.M, K // 2)), self.sbuf.view(torch.uint8, (self.agemm.sf_bytes(self.M, K),))
+
+    def row_linear(self, layer, x_local):
+        """row-parallel linear: quantise the local K shard, GEMM with the scatter epilogue, barrier + slot sum -> [M/W, H]"""
+        qx, sfx, sc = layer.quantize_input(x_local, fused=True)
+        self.group.gemm_scatter(qx, layer.W, sfx, layer.scale_w, sc * layer.scale, self.recv, self.Mloc)
+        out = self.out[self.flip]
+        self.flip ^= 1
+        return self.group.reduce(self.recv, self.Mloc, self.H, out, channel=0)
+
 
 def reference_layer_forward(layer: "ArcDecoderLayer", h: torch.Tensor) -> torch.Tensor:
     """The same decoder layer in plain fp32 torch with the UNQUANTISED weights (needs keep_ref=True): test oracle."""
@@ -207,6 +270,32 @@ class ArcPrefillModel(torch.nn.Module):
         for layer in self.layers:
             h = layer(h)
         return h
+
+    def enable_seq_parallel(self, dev, tokens: int):
+        """Collective: set up the peer-memory exchange for `tokens` = B * S tokens per forward (tensor parallel, world > 1)."""
+        l0 = self.layers[0]
+        if not all(l.fused for l in self.layers):
+            raise ValueError("the sequence-parallel path runs the fused launches")
+        self.xc = SeqParallelExchange(self.cfg, dev, tokens, max(max(l.ke_qkv, l.ke_gu) for l in self.layers), l0.agemm)
+        return self.xc
+
+    @torch.no_grad()
+    def forward_seq_parallel(self, h, gather_output: bool = True):
+        """h [B, S, H] replicated on every rank (as forward takes it); the residual stream is kept token-sharded through
+        the whole stack.  Returns the full [B, S, H] (one all-gather at the very end) or this rank's [M/W, H] rows."""
+        B, S, H = h.shape
+        xc = self.xc
+        r = xc.group.rank
+        h_loc = h.reshape(B * S, H)[r * xc.Mloc:(r + 1) * xc.Mloc].contiguous()
+        pending = None
+        for layer in self.layers:
+            h_loc, pending = layer.forward_sp(xc, h_loc, pending, B, S)
+        h_loc = h_loc + pending
+        if not gather_output:
+            return h_loc
+        full = torch.empty((B * S, H), dtype=h_loc.dtype, device=h_loc.device)
+        dist.all_gather_into_tensor(full, h_loc)
+        return full.view(B, S, H)
 
     def linear_flops(self, tokens: int) -> float:
         c = self.cfg

@@ -106,3 +106,33 @@ def test_gemm_linearity_full_size():
     y2 = agemm.matmul(qa, qb, sfa2, sfb, 2e-4)
     torch.cuda.synchronize()
     assert torch.equal(y1, y2)
+
+
+def test_tensor_scale_is_read_on_the_device_and_captures_in_a_cuda_graph():
+    """`scale` given as a 1-element CUDA tensor must reach the kernel as a device pointer: no .item() (host sync), so the
+    call can be captured in a CUDA graph -- and the replay must see a NEW value written to the tensor afterwards.  (The
+    reference converts the tensor to `const float` on the host, kernels/src/bindings.cpp:104.)"""
+    from arcquant_b200 import agemm
+    M, N, K = 256, 512, 1088
+    g = torch.Generator(device="cuda").manual_seed(3)
+    qa = torch.randint(0, 256, (M, K // 2), dtype=torch.uint8, device="cuda", generator=g)
+    qb = torch.randint(0, 256, (N, K // 2), dtype=torch.uint8, device="cuda", generator=g)
+    sfa = torch.randint(0x30, 0x40, (agemm.sf_bytes(M, K),), dtype=torch.uint8, device="cuda", generator=g)
+    sfb = torch.randint(0x30, 0x40, (agemm.sf_bytes(N, K),), dtype=torch.uint8, device="cuda", generator=g)
+    scale = torch.tensor([1e-3], dtype=torch.float32, device="cuda")
+    out = torch.empty((M, N), dtype=torch.bfloat16, device="cuda")
+    agemm.matmul(qa, qb, sfa, sfb, scale, out=out)          # warm-up outside the capture (tensor maps, attributes)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            agemm.matmul(qa, qb, sfa, sfb, scale, out=out)  # a host read of `scale` here would invalidate the capture
+    torch.cuda.current_stream().wait_stream(side)
+    scale.fill_(2e-3)
+    graph.replay()
+    torch.cuda.synchronize()
+    want = agemm.matmul(qa, qb, sfa, sfb, 2e-3)
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)

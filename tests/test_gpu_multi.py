@@ -99,3 +99,25 @@ def test_two_devices_from_one_process():
         res.append((qx.cpu(), y.cpu()))
     assert torch.equal(res[0][0], res[2][0]) and torch.equal(res[1][0], res[3][0])
     assert torch.equal(res[0][1], res[2][1]) and torch.equal(res[1][1], res[3][1])
+
+
+def test_two_rank_sequence_parallel_prefill_matches_allreduce_path():
+    """scripts/prefill_bench.py on 2 ranks: the sequence-parallel stack over peer memory (scatter-epilogue GEMMs, slot sums,
+    gathered codes, fused residual add / norm / quantise, CUDA-graph replay) against the replicated-activation + NCCL
+    all-reduce path on the SAME shards: only the reduction's rounding differs (fp32 slot sum vs bf16 ring)."""
+    _need2()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "scripts", "prefill_bench.py"), "--model", "tiny", "--bsz", "2",
+           "--seq", "512", "--steps", "2", "--warmup", "1", "--check"]
+    p = subprocess.Popen(cmd, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, start_new_session=True)
+    try:
+        out, err = p.communicate(timeout=240)
+    except subprocess.TimeoutExpired:
+        import signal
+        os.killpg(p.pid, signal.SIGKILL)
+        out, err = p.communicate()
+        pytest.fail("2-rank prefill timed out: " + err[-1500:])
+    assert p.returncode == 0, err[-2000:]
+    res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert "sequence parallel over peer memory" in res["config"]["parallelism"], res
+    assert res["check"]["finite"] and res["check"]["rel_fro_vs_allreduce_path"] < 2e-2, res["check"]
