@@ -176,8 +176,9 @@ class ArcDecoderLayer(torch.nn.Module):
     # ---- sequence-parallel form over peer memory (SeqParallelExchange below) ----
     @torch.no_grad()
     def forward_sp(self, xc: "SeqParallelExchange", h_loc, pending, B, S):
-        """This rank owns tokens [rank * M / W, +M / W) of the residual stream (h_loc [M/W, H]); `pending` is the previous
-        layer's reduce-scattered down_proj output, not yet added.  Per layer: 2 x (norm + quantise of the own tokens ->
+        """xc = None: the whole token range on this rank (one GPU, or replicated activations with `_row`'s all-reduce) -- the
+        same chain without the exchange steps.  Otherwise this rank owns tokens [rank * M / W, +M / W) of the residual
+        stream (h_loc [M/W, H]); `pending` is the previous layer's (reduce-scattered) down_proj output, not yet added.  Per layer: 2 x (norm + quantise of the own tokens ->
         gather of codes + scale blocks by peer stores -> column-parallel GEMM) and 2 x (row-parallel GEMM whose epilogue
         scatters into the owners' slots -> barrier + slot sum); both residual adds ride in front of the norms
         (add_rmsnorm_quantize_x).  No NCCL call, no torch pass over the residual stream.  Returns (h_loc, pending)."""
@@ -187,18 +188,18 @@ class ArcDecoderLayer(torch.nn.Module):
             qx, sfx = ag.rmsnorm_quantize_x(h_loc, self.norm1, eps, self.idx_h1, self.ke_qkv)
         else:
             qx, sfx, h_loc = ag.add_rmsnorm_quantize_x(pending, h_loc, self.norm1, eps, self.idx_h1, self.ke_qkv)
-        qf, sff = xc.gather(qx, sfx, H + self.ke_qkv)
+        qf, sff = (qx, sfx) if xc is None else xc.gather(qx, sfx, H + self.ke_qkv)
         qkv = ag.matmul(qf, self.qkv_w[0], sff, self.qkv_w[1], self.one, col_scale=self.qkv_w[2], bias=self.qkv_bias)
         q, k, v = qkv.split(H // W, dim=1)
         shp = (B, S, self.local_heads, self.head_dim)
         q, k, v = (t.reshape(shp).transpose(1, 2) for t in (q, k, v))
         q, k = _rope(q, k)
         a = F.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(M, -1).contiguous()
-        o_loc = xc.row_linear(self.o, a)
+        o_loc = self._row(self.o, a) if xc is None else xc.row_linear(self.o, a)
         qx, sfx, h_loc = ag.add_rmsnorm_quantize_x(o_loc, h_loc, self.norm2, eps, self.idx_h2, self.ke_gu)
-        qf, sff = xc.gather(qx, sfx, H + self.ke_gu)
+        qf, sff = (qx, sfx) if xc is None else xc.gather(qx, sfx, H + self.ke_gu)
         m = ag.matmul(qf, self.gu_w[0], sff, self.gu_w[1], self.one, col_scale=self.gu_w[2], epilogue=ag.EPILOGUE_SWIGLU)
-        return h_loc, xc.row_linear(self.down, m)
+        return h_loc, (self._row(self.down, m) if xc is None else xc.row_linear(self.down, m))
 
 
 class SeqParallelExchange:
@@ -267,6 +268,15 @@ class ArcPrefillModel(torch.nn.Module):
 
     @torch.no_grad()
     def forward(self, h):
+        c = self.cfg
+        if all(l.fused for l in self.layers) and 2048 <= c.hidden <= 8192 and c.hidden % 64 == 0 and \
+                all(l.ke_qkv % 64 == 0 and l.ke_gu % 64 == 0 for l in self.layers):
+            # every residual add rides in front of the next norm (add_rmsnorm_quantize_x): no torch pass over the stream
+            B, S, H = h.shape
+            x, pending = h.reshape(B * S, H), None
+            for layer in self.layers:
+                x, pending = layer.forward_sp(None, x, pending, B, S)
+            return (x + pending).view(B, S, H)
         for layer in self.layers:
             h = layer(h)
         return h

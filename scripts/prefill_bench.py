@@ -66,7 +66,7 @@ def main():
         run()
     torch.cuda.synchronize()
     graph = None
-    if sp and not args.no_graph:   # a shard's kernels are short: replay the whole forward (only this library's kernels + torch glue)
+    if (sp or world == 1) and not args.no_graph:   # a shard's kernels are short: replay the whole forward (only this library's kernels + torch glue)
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -96,7 +96,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item()) / args.steps
     if rank == 0:
-        par = "single GPU"
+        par = "single GPU, %s" % ("CUDA-graph replay" if graph is not None else "launched from Python")
         if world > 1:
             par = ("tp%d, sequence parallel over peer memory (scatter-epilogue GEMMs + slot sums, codes gathered by peer stores, "
                    "residual adds fused into the norms), %s" % (world, "CUDA-graph replay" if graph is not None else "launched from Python")

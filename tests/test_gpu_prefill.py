@@ -122,3 +122,21 @@ def test_prefill_runs_on_calibration_artifacts(tmp_path):
     torch.cuda.synchronize()
     d, r = (y.float() - h.float()), (ref - h.float())
     assert float((d - r).norm() / r.norm()) < 0.35
+
+
+def test_chained_forward_equals_layer_by_layer():
+    """ArcPrefillModel.forward carries the down_proj output as a pending residual and adds it inside the NEXT norm's kernel
+    (add_rmsnorm_quantize_x); calling the layers one by one does the adds in torch.  Same bits (the fused add is torch's
+    bf16 add), for a model with q/k/v biases (bias epilogue) and one without."""
+    dev = torch.device("cuda:0")
+    for name in ("tiny", "llama-3-8b"):
+        cfg = prefill.PrefillConfig.named(name, layers=2)
+        model = prefill.ArcPrefillModel(cfg, dev, seed=7)
+        g = torch.Generator(device=dev).manual_seed(2)
+        h = torch.randn(2, 192, cfg.hidden, device=dev, generator=g).to(torch.bfloat16)
+        y = model(h)
+        z = h
+        for layer in model.layers:
+            z = layer(z)
+        torch.cuda.synchronize()
+        assert torch.equal(y, z), name
