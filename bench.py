@@ -83,41 +83,65 @@ class ClockSampler:
 
     def __init__(self, gpu_index):
         self.idx = gpu_index
-        self.proc = None
+        self.proc, self.lines, self.marks, self.thread = None, [], {}, None
 
     def start(self):
+        """Started EARLY (before the layer is built): nvidia-smi needs ~0.1-0.3 s before its first line, and the driver's
+        timed region can be as short as 20 x 0.9 ms.  Lines are stamped on arrival; stop() picks by time window."""
+        import threading
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "10"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, bufsize=1)
         except Exception:
             self.proc = None
+            return
+
+        def reader():
+            try:
+                for line in self.proc.stdout:
+                    self.lines.append((time.perf_counter(), line))
+            except Exception:
+                pass
+        self.thread = threading.Thread(target=reader, daemon=True)
+        self.thread.start()
+
+    def mark(self, name):
+        self.marks[name] = time.perf_counter()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.03)
         self.proc.terminate()
         try:
-            out, _ = self.proc.communicate(timeout=5)
+            self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-            out = ""
-        sm, mx, pw, reasons = [], [], [], set()
+        if self.thread is not None:
+            self.thread.join(timeout=2)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
+        rows = []
+        for t, line in list(self.lines):
             f = [c.strip() for c in line.split(",")]
             if len(f) < 9:
                 continue
             try:
-                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+                rows.append((t, float(f[1]), float(f[2]), float(f[3]), [n for n, v in zip(names, f[5:9]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for n, v in zip(names, f[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+        t0, t1, l0 = self.marks.get("t0"), self.marks.get("t1"), self.marks.get("load0")
+        timed = [r for r in rows if t0 is not None and t1 is not None and t0 <= r[0] <= t1 + 0.012]   # a line reports the ~10 ms before it
+        # a short timed region holds 0-2 samples at nvidia-smi's pace: then the window is the same step loop under load, from
+        # the first of the 100 untimed steps that lead into the timed region to its end
+        load = [r for r in rows if l0 is not None and t1 is not None and l0 <= r[0] <= t1 + 0.012]
+        use, window = (timed, "timed region") if len(timed) >= 3 else (load, "100 untimed steps + the timed region (same step loop, back to back)")
+        if not use:
+            use, window = rows[-5:], "last samples before the end of the timed region"
+        reasons = sorted({n for r in use for n in r[4]})
+        return {"sm_mhz": statistics.median([r[1] for r in use]) if use else None, "sm_max_mhz": max(r[2] for r in use) if use else None,
+                "power_w_max": max(r[3] for r in use) if use else None, "samples": len(use), "samples_in_timed_region": len(timed),
+                "window": window, "reasons": reasons}
 
 
 # ---- the reference's CPU implementation of the path (fake-quant), bounded sample -----------------------------------
@@ -618,6 +642,9 @@ def run_native(args):
         dist.init_process_group("nccl", device_id=dev)
     from arcquant_b200 import agemm
     peaks = load_peaks()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     M = args.tokens
     tp_mode = world > 1 and args.parallelism in ("tp", "tp-ar")
     slabs = args.slabs if (tp_mode and args.parallelism == "tp") else 1
@@ -688,17 +715,22 @@ def run_native(args):
         else:
             layer.step()
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     n0 = agemm.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # 100 more untimed steps straight into the timed ones: nvidia-smi reports every ~10 ms and the driver's timed region can
+    # be 20 x 0.9 ms, so the clock / throttle samples are taken over this window of the SAME step loop under the SAME load
+    # (the samples that fall inside the timed region itself are counted separately)
+    sampler.mark("load0")
+    for _ in range(100):
+        run_step()
     barrier()
+    sampler.mark("t0")
     e0.record()
     for _ in range(args.steps):
         run_step()
     e1.record()
     barrier()
+    sampler.mark("t1")
     ms = e0.elapsed_time(e1)
     launches = agemm.launch_count() - n0
     clocks = sampler.stop() if rank == 0 else None
