@@ -91,7 +91,7 @@ class ClockSampler:
         import threading
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "10"],
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, bufsize=1)
         except Exception:
             self.proc = None
@@ -112,7 +112,7 @@ class ClockSampler:
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.03)
+        time.sleep(0.08)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -130,14 +130,17 @@ class ClockSampler:
                 rows.append((t, float(f[1]), float(f[2]), float(f[3]), [n for n, v in zip(names, f[5:9]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-        t0, t1, l0 = self.marks.get("t0"), self.marks.get("t1"), self.marks.get("load0")
-        timed = [r for r in rows if t0 is not None and t1 is not None and t0 <= r[0] <= t1 + 0.012]   # a line reports the ~10 ms before it
-        # a short timed region holds 0-2 samples at nvidia-smi's pace: then the window is the same step loop under load, from
-        # the first of the 100 untimed steps that lead into the timed region to its end
-        load = [r for r in rows if l0 is not None and t1 is not None and l0 <= r[0] <= t1 + 0.012]
-        use, window = (timed, "timed region") if len(timed) >= 3 else (load, "100 untimed steps + the timed region (same step loop, back to back)")
+        t0, t1 = self.marks.get("t0"), self.marks.get("t1")
+        # a line describes the ~20 ms before it arrives; the driver's timed region can be as short as 20 x 0.9 ms, so the
+        # window is the timed region plus one sampling period, and -- if nvidia-smi's pace put no line there -- the first
+        # lines after it (the clocks the GPU left the timed loop with).  No extra load is run for the sampler's sake: 100
+        # more steps in front of the timed ones were measured to move the step from burst (0.878 ms) to power-capped (0.998 ms)
+        timed = [r for r in rows if t0 is not None and t1 is not None and t0 <= r[0] <= t1 + 0.025]
+        use, window = timed, "timed region (+ one 20 ms sampling period)"
+        if not use and t1 is not None:
+            use, window = [r for r in rows if r[0] > t1][:3], "first samples after the timed region (none fell inside it)"
         if not use:
-            use, window = rows[-5:], "last samples before the end of the timed region"
+            use, window = rows[-3:], "last samples taken"
         reasons = sorted({n for r in use for n in r[4]})
         return {"sm_mhz": statistics.median([r[1] for r in use]) if use else None, "sm_max_mhz": max(r[2] for r in use) if use else None,
                 "power_w_max": max(r[3] for r in use) if use else None, "samples": len(use), "samples_in_timed_region": len(timed),
@@ -717,12 +720,6 @@ def run_native(args):
 
     n0 = agemm.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # 100 more untimed steps straight into the timed ones: nvidia-smi reports every ~10 ms and the driver's timed region can
-    # be 20 x 0.9 ms, so the clock / throttle samples are taken over this window of the SAME step loop under the SAME load
-    # (the samples that fall inside the timed region itself are counted separately)
-    sampler.mark("load0")
-    for _ in range(100):
-        run_step()
     barrier()
     sampler.mark("t0")
     e0.record()
