@@ -48,6 +48,22 @@ class PeerBuffer:
         """ctypes array of `world` device pointers (what the `peer_*` arguments of the C ABI take)."""
         return self._arr
 
+    def close(self):
+        """Unmap the peers' copies and free the local one.  NOT collective, but every rank must have finished using the
+        buffer (a barrier of the caller's choice): a peer that still stores into freed memory faults.  Idempotent."""
+        L = _lib.load()
+        local, self.local = self.local, 0
+        if not local:
+            return
+        self.tensor = None
+        with torch.cuda.device(self.group.device):
+            if getattr(self.group, "_local", None) is None:          # multi-process: the other entries are IPC mappings
+                for r, p in enumerate(self.ptrs):
+                    if r != self.group.rank and p:
+                        L.arcq_peer_close(ctypes.c_void_p(p))
+            L.arcq_peer_free(ctypes.c_void_p(local))
+        self.ptrs = []
+
     def view(self, dtype, shape, byte_offset: int = 0):
         n = 1
         for s in shape:

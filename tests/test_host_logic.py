@@ -138,3 +138,42 @@ def test_calibration_artifacts_roundtrip_in_the_reference_schema(tmp_path):
     with pytest.raises(ValueError):
         C.validate(ri, {**sn, k: 100})
     assert C.select_num_for(4096, 0.06) == 256 and C.select_num_for(4096, 0.0) == 0
+
+
+def test_peer_constants_match_the_header_and_bad_arguments_are_rejected_without_a_gpu():
+    """arcquant_b200/peer.py mirrors the limits of include/arcq.h; the argument checks of the peer entry points run before
+    anything touches a device (no launch happens for a rejected call)."""
+    import ctypes
+    import os
+    import re
+    from arcquant_b200 import _lib, peer as P
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "arcq.h")).read()
+    macro = lambda n: int(re.search(r"#define\s+%s\s+(\d+)" % n, hdr).group(1))
+    assert (P.MAX_PEERS, P.FLAG_BYTES, P.CHANNELS) == (macro("ARCQ_MAX_PEERS"), macro("ARCQ_PEER_FLAG_BYTES"), macro("ARCQ_PEER_CHANNELS"))
+    assert macro("ARCQ_PEER_HANDLE_BYTES") == 64
+    assert P.world_bytes(8, 1024, 4096) == 8 * 1024 * 4096 * 2
+    L = _lib.load()
+    fake = (ctypes.c_void_p * 2)(0x10000, 0x20000)
+    a = ctypes.c_void_p(0x1000)
+    # rows_per_rank must be a multiple of 128 covering M
+    assert L.arcq_gemm_nvfp4_scatter(a, a, a, a, 256, 128, 64, 1.0, None, None, fake, 2, 0, 64, 0, None) == -1
+    assert "rows_per_rank" in _lib.last_error()
+    assert L.arcq_gemm_nvfp4_scatter(a, a, a, a, 512, 128, 64, 1.0, None, None, fake, 2, 0, 128, 0, None) == -1
+    # rank outside the world, too many peers, misaligned peer pointer
+    assert L.arcq_peer_reduce(a, fake, 2, 2, 0, 8, 8, 0, a, 0, None) == -1
+    assert L.arcq_peer_reduce(a, fake, 9, 0, 0, 8, 8, 0, a, 0, None) == -1
+    odd = (ctypes.c_void_p * 2)(0x10000, 0x20004)
+    assert L.arcq_peer_reduce(a, odd, 2, 0, 0, 8, 8, 0, a, 0, None) == -1 and "aligned" in _lib.last_error()
+    # cols not a multiple of 8, channel out of range, segment sizes not multiples of 16
+    assert L.arcq_peer_reduce(a, fake, 2, 0, 0, 8, 12, 0, a, 0, None) == -1
+    assert L.arcq_peer_reduce(a, fake, 2, 0, P.CHANNELS, 8, 8, 0, a, 0, None) == -1
+    assert L.arcq_peer_allgather(a, 40, fake, 0, None, 0, None, 0, fake, 2, 0, 0, None) == -1
+    assert L.arcq_peer_allgather(a, 32, fake, 8, None, 0, None, 0, fake, 2, 0, 0, None) == -1
+    # bias: alignment and the SwiGLU exclusion are checked before any launch
+    assert L.arcq_gemm_nvfp4_ex2(a, a, a, a, 128, 256, 64, 1.0, None, None, ctypes.c_void_p(0x1008), 0, a, 0, None) == -1
+    assert L.arcq_gemm_nvfp4_ex2(a, a, a, a, 128, 256, 64, 1.0, None, None, ctypes.c_void_p(0x2000), 1, a, 0, None) == -1
+    assert "SwiGLU" in _lib.last_error()
+    # fused residual add: null / misaligned residual
+    i16 = ctypes.c_void_p(0x3000)
+    assert L.arcq_add_rmsnorm_quantize_x(a, None, a, 1e-6, 4, 4096, i16, 256, a, a, a, None) == -1
+    assert L.arcq_add_rmsnorm_quantize_x(a, a, a, 1e-6, 4, 1024, i16, 64, a, a, a, None) == -3   # H outside the reduction tree's range
