@@ -278,3 +278,32 @@ def test_torchref_matches_c_oracle(O):
     assert np.array_equal(T.sf_offsets(torch.arange(M), K).numpy(), O.sf_valid_offsets(M, K))
     r = T.sample_rows(1000)
     assert r[0] == 0 and r[-1] == 999 and all(((r >= b * 128) & (r < b * 128 + 128)).sum() >= 1 for b in range(8))
+
+
+def test_bf16_add_restatement_is_torchs_bf16_add():
+    """The fused residual add (arcq_add_rmsnorm_quantize_x) and the bias epilogue (arcq_gemm_nvfp4_ex2) are specified as
+    torch's bf16 `a + b`: an fp32 add rounded to nearest even.  tests/test_gpu_addnorm.py checks the kernel against the
+    numpy restatement `f32_to_bf16_bits(f32(a) + f32(b))`; this pins that restatement to torch itself on the CPU, on random
+    values, exact cancellations, sums that need more than 8 bits, ties, overflow to inf and subnormals."""
+    import torch
+    g = torch.Generator().manual_seed(0)
+    a = (torch.randn(1 << 16, generator=g) * 8).to(torch.bfloat16)
+    b = (torch.randn(1 << 16, generator=g) * 8).to(torch.bfloat16)
+    b[::5] = -a[::5]
+    b[1::7] = (a[1::7].float() * -1.0078125).to(torch.bfloat16)
+    a[2::11] *= 2.0 ** 20
+    a[3::13] = torch.tensor(3.3895e38).to(torch.bfloat16)          # near the top of the range: a + a overflows
+    b[3::13] = a[3::13]
+    a[4::17] = torch.tensor(1e-39).to(torch.bfloat16)              # subnormal operands
+    # every pair of the 2^8 x 2^8 mantissa/exponent neighbourhood around 1.0: all rounding ties of the add
+    lo = torch.arange(0x3f00, 0x4000, dtype=torch.int32).to(torch.int16).view(torch.bfloat16)
+    a = torch.cat((a, lo.repeat_interleave(lo.numel())))
+    b = torch.cat((b, (lo.float() * 2.0 ** -7).to(torch.bfloat16).repeat(lo.numel())))
+    want = (a + b).view(torch.int16).numpy().view(np.uint16)
+    ab = a.view(torch.int16).numpy().view(np.uint16)
+    bb = b.view(torch.int16).numpy().view(np.uint16)
+    with np.errstate(over="ignore"):
+        got = oracle.f32_to_bf16_bits(oracle.bf16_bits_to_f32(ab) + oracle.bf16_bits_to_f32(bb))
+    nan = np.isnan(oracle.bf16_bits_to_f32(want))
+    assert np.array_equal(got[~nan], want[~nan])
+    assert np.isnan(oracle.bf16_bits_to_f32(got[nan])).all()
