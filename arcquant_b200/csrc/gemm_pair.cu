@@ -70,6 +70,7 @@ struct PParams {
   __nv_bfloat16 *peer_d[ARCQ_MAX_PEERS];
   int rs_rows, rs_rank;
   const __nv_bfloat16 *col_bias;   // nullable bf16 [N] (plain epilogue only): torch's `y + bias` on the rounded output
+  int raster_gm;                   // 0: tile t -> (t % ptiles_m, t / ptiles_m); g > 0: groups of g row tiles, column tiles inside a group
 };
 
 // bf16(silu(g)) * u exactly as torch computes `F.silu(g) * u` on bf16 tensors: silu in fp32 (x / (1 + exp(-x)), IEEE
@@ -118,6 +119,19 @@ __device__ __forceinline__ void load_col_scales(float (&sreg)[NREG], const float
     const int c = col0 + r * 32 + lane;
     sreg[r] = (cs && c < N) ? __fmul_rn(alpha, __ldg(cs + c)) : alpha;
   }
+}
+
+// persistent tile order.  Default: row tiles fastest (a wave of 74 pairs covers every row tile of 2-3 column tiles).  Grouped
+// (arcq_set_option "gemm_raster" = g): g row tiles x all column tiles per group, row tiles fastest inside a group, so a
+// wave touches ~g row panels of A and ~74/g column panels of B (a smaller unique footprint per wave)
+__device__ __forceinline__ void tile_coords(const PParams &p, int t, int &pm, int &pn) {
+  if (p.raster_gm <= 0) { pm = t % p.ptiles_m; pn = t / p.ptiles_m; return; }
+  const int per_group = p.raster_gm * p.ptiles_n;
+  const int group = t / per_group, first_m = group * p.raster_gm;
+  const int gsz = min(p.raster_gm, p.ptiles_m - first_m);
+  const int r = t - group * per_group;
+  pm = first_m + r % gsz;
+  pn = r / gsz;
 }
 
 // SWIGLU: the 256 columns of a pair tile are 128 "gate" columns followed by the 128 "up" columns of the SAME 128
@@ -176,7 +190,8 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     PROF(long long pw = 0, pw_n = 0, pt0 = clock64();)
     uint32_t ready = ptx::mbar_test(&empty[0], 1);
     for (int t = pair_id; t < num_ptiles; t += num_pairs) {
-      const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
+      int pm, pn;
+      tile_coords(p, t, pm, pn);
       const int mblk = pm * 2 + (int)rank;        // this CTA's 128-row block of A / SFA
       for (int kb = 0; kb < nkb; ++kb, ++it) {
         const int s = it % STAGES;
@@ -277,7 +292,8 @@ gemm_nvfp4_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     uint32_t tile_it = 0;
     PROF(long long ew = 0, eld = 0, et0 = clock64();)
     for (int t = pair_id; t < num_ptiles; t += num_pairs, ++tile_it) {
-      const int pm = t % p.ptiles_m, pn = t / p.ptiles_m;
+      int pm, pn;
+      tile_coords(p, t, pm, pn);
       // first tile column of this warp's register block (input columns of the GEMM, for the per-column scales)
       const int in_col0 = pn * kBN + (SWIGLU ? half * (HC / 2) : half * HC);
       const int out_col0 = SWIGLU ? pn * (kBN / 2) + half * (HC / 2) : in_col0;
@@ -421,7 +437,7 @@ static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, con
     if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
     max_pairs[dev] = n;
   }
-  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0, (const __nv_bfloat16 *)col_bias};
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0, (const __nv_bfloat16 *)col_bias, options().gemm_raster};
   if (sc) {
     for (int i = 0; i < ARCQ_MAX_PEERS; ++i) p.peer_d[i] = (__nv_bfloat16 *)sc->peer_recv[i < sc->world ? i : sc->world - 1];
     p.rs_rows = sc->rows_per_rank;

@@ -644,6 +644,8 @@ def run_native(args):
             os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version there)
         dist.init_process_group("nccl", device_id=dev)
     from arcquant_b200 import agemm
+    for kv in args.option:
+        agemm.set_option(*kv.split("=", 1))
     peaks = load_peaks()
     sampler = ClockSampler(local)
     if rank == 0:
@@ -889,6 +891,8 @@ def run_native(args):
         "parity_check": parity, "cpu_baseline": cpu, "clocks": clocks, "prefill_config3": prefill_res,
         "binding": agemm.BACKEND,
     }
+    if args.option:
+        out["options"] = args.option
     if tp_mode:
         out["exchange"] = "peer" if layer.peer is not None else "nccl"
         if layer.peer_note:
@@ -979,6 +983,8 @@ def main():
     ap.set_defaults(peer=True)
     ap.add_argument("--no-check", action="store_true", help="skip the oracle check of the last step's outputs")
     ap.add_argument("--no-prefill", action="store_true", help="skip the config-3 prefill line (N=1)")
+    ap.add_argument("--option", action="append", default=[], metavar="NAME=VALUE",
+                    help="arcq_set_option override for A/B runs (every choice computes the same result), e.g. gemm_raster=8")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-tokens", type=int, default=2048)
     ap.add_argument("--cpu-reps", type=int, default=5)

@@ -210,3 +210,21 @@ def test_bias_epilogue_equals_torch_add(arcq_option, variant, M, N, K):
     assert torch.equal(y1, y0 + bias), "%s M=%d N=%d K=%d" % (variant, M, N, K)
     with pytest.raises(RuntimeError):
         agemm.matmul(qa, qb, sfa, sfb, 1e-3, bias=bias[:-8].contiguous())
+
+
+@pytest.mark.parametrize("g", [1, 3, 8, 64])
+@pytest.mark.parametrize("M,N,K", [(8192, 4096, 4352), (2048 + 130, 7168 + 8, 1088), (8192, 28672, 576)])
+def test_grouped_tile_order_of_the_pair_kernel(arcq_option, g, M, N, K):
+    """arcq_set_option("gemm_raster", g): the persistent cta_group::2 kernel walks its tiles in groups of g row tiles (a ragged
+    last group included); every tile must still be computed exactly once -- bit-identical to the default order."""
+    from arcquant_b200 import agemm
+    arcq_option("gemm_pair", 1)
+    qa, sfa = _rand_operand(M, K, 11)
+    qb, sfb = _rand_operand(N, K, 12)
+    y0 = agemm.matmul(qa, qb, sfa, sfb, 1e-3)
+    arcq_option("gemm_raster", g)
+    y1 = agemm.matmul(qa, qb, sfa, sfb, 1e-3)
+    torch.cuda.synchronize()
+    assert torch.equal(y0, y1), "gemm_raster=%d M=%d N=%d K=%d" % (g, M, N, K)
+    if g == 8:
+        _assert_ok(y1, qa, sfa, qb, sfb, 1e-3, "raster 8 M=%d N=%d K=%d" % (M, N, K), per_block=1)
