@@ -32,7 +32,7 @@ struct Options {
   int gemm_pair;       // -1 = by shape, 0 = never, 1 = always use the cta_group::2 kernel
   int gemm_bn;         // 0 = by shape, 128 / 256 = tile width of the single-CTA kernel
   int gemm_splitk;     // -1 = by shape, 0 = never, >= 2 = forced number of K splits of the small-M kernel
-  int gemm_raster;     // cta_group::2 kernel: 0 = tiles walk M fastest (default), g > 0 = groups of g row tiles x all column tiles
+  int gemm_raster;     // cta_group::2 kernel tile order: -1 = by shape, 0 = row tiles fastest, g > 0 = groups of g row tiles x all column tiles
 };
 Options &options();
 

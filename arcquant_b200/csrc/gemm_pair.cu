@@ -437,7 +437,10 @@ static int launch_gemm_pair_t(const void *a, const void *b, const void *sfa, con
     if (n < 1) { set_error("no CTA pair fits on this device"); return ARCQ_ENOSUP; }
     max_pairs[dev] = n;
   }
-  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0, (const __nv_bfloat16 *)col_bias, options().gemm_raster};
+  PParams p{(__nv_bfloat16 *)d, alpha_dev, col_scale, alpha, M, N, K, ldd, (M + 255) / 256, (N + 255) / 256, nullptr, {}, 0, 0, (const __nv_bfloat16 *)col_bias, 0};
+  // tile order, measured inside the bench step (profiles/r2_gemm_raster_ab.log): groups of 16 row tiles are 1-3 % faster for
+  // N = 4096 / 6144 (down 170.9 -> 165.6 us, o 64.5 -> 63.6, q+k+v 95.5 -> 94.7) and 2-9 % slower for N = 28672: narrow outputs only
+  p.raster_gm = options().gemm_raster >= 0 ? options().gemm_raster : (p.ptiles_n <= 32 ? 16 : 0);
   if (sc) {
     for (int i = 0; i < ARCQ_MAX_PEERS; ++i) p.peer_d[i] = (__nv_bfloat16 *)sc->peer_recv[i < sc->world ? i : sc->world - 1];
     p.rs_rows = sc->rows_per_rank;

@@ -27,7 +27,7 @@ int current_device() {
 }
 
 Options &options() {
-  static Options o = {{0, 0, 0, 0, 0}, 3, -1, 0, -1, 0};
+  static Options o = {{0, 0, 0, 0, 0}, 3, -1, 0, -1, -1};
   return o;
 }
 
@@ -72,7 +72,7 @@ extern "C" int arcq_set_option(const char *name, const char *value) {
   if (!strcmp(name, "gemm_pair")) { o.gemm_pair = has ? iv : -1; return ARCQ_OK; }
   if (!strcmp(name, "gemm_bn")) { o.gemm_bn = has ? iv : 0; return ARCQ_OK; }
   if (!strcmp(name, "gemm_splitk")) { o.gemm_splitk = has ? iv : -1; return ARCQ_OK; }
-  if (!strcmp(name, "gemm_raster")) { o.gemm_raster = has && iv > 0 ? iv : 0; return ARCQ_OK; }
+  if (!strcmp(name, "gemm_raster")) { o.gemm_raster = has ? (iv > 0 ? iv : 0) : -1; return ARCQ_OK; }
   set_error("arcq_set_option: unknown option '%s'", name);
   return ARCQ_EINVAL;
 }

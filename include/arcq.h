@@ -221,7 +221,7 @@ int arcq_peer_allgather(const void *src0, int64_t bytes0, void *const *peer_dst0
 /* name = value override of a shape-driven kernel choice ("" = back to the default).  Every choice computes the same
  * result; the parity tests force each tile organisation through this.  Options: "quant_tile" = "R,threads,S,RT,CTAs/SM",
  * "quant_family" = 3 | 1, "gemm_pair" = 0 | 1, "gemm_bn" = 128 | 256, "gemm_splitk" = 0 | 2 | 4 | 8, "gemm_raster" = 0 | g (tile order of the
- * cta_group::2 kernel: row tiles fastest, or groups of g row tiles).  The product
+ * cta_group::2 kernel: row tiles fastest, or groups of g row tiles; default by shape).  The product
  * library reads NO environment variables and has no switch that skips work. */
 int arcq_set_option(const char *name, const char *value);
 

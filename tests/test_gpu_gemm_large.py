@@ -212,7 +212,7 @@ def test_bias_epilogue_equals_torch_add(arcq_option, variant, M, N, K):
         agemm.matmul(qa, qb, sfa, sfb, 1e-3, bias=bias[:-8].contiguous())
 
 
-@pytest.mark.parametrize("g", [1, 3, 8, 64])
+@pytest.mark.parametrize("g", [1, 3, 8, 16, 64])
 @pytest.mark.parametrize("M,N,K", [(8192, 4096, 4352), (2048 + 130, 7168 + 8, 1088), (8192, 28672, 576)])
 def test_grouped_tile_order_of_the_pair_kernel(arcq_option, g, M, N, K):
     """arcq_set_option("gemm_raster", g): the persistent cta_group::2 kernel walks its tiles in groups of g row tiles (a ragged
@@ -221,6 +221,7 @@ def test_grouped_tile_order_of_the_pair_kernel(arcq_option, g, M, N, K):
     arcq_option("gemm_pair", 1)
     qa, sfa = _rand_operand(M, K, 11)
     qb, sfb = _rand_operand(N, K, 12)
+    arcq_option("gemm_raster", 0)
     y0 = agemm.matmul(qa, qb, sfa, sfb, 1e-3)
     arcq_option("gemm_raster", g)
     y1 = agemm.matmul(qa, qb, sfa, sfb, 1e-3)
