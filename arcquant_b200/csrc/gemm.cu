@@ -418,9 +418,16 @@ extern "C" int arcq_gemm_nvfp4_ex2(const void *a, const void *b, const void *sfa
   const int splits = o.gemm_splitk >= 0 ? o.gemm_splitk : splitk_choice((int)M, (int)N, (int)K);
   if (splits >= 2 && (M <= 1024 || o.gemm_splitk >= 2))
     return launch_gemm_splitk(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, d, ldd, splits, st, col_bias_dev);
-  // cta_group::2 kernel for shapes with at least one 256 x 256 tile per SM pair
+  // Kernel choice for what split-K did not take, from the measured A/B on the config-2 shapes (profiles/r2_midm_kernel_choice_ab.log):
+  //  * at most one wave of 128 x 128 tiles (<= SM count): the single-CTA kernel with 128-wide tiles puts the most SMs on the
+  //    problem -- q/o at M <= 512: 10.0-10.6 us against 13.1-13.7 us with 256-wide tiles, k/v up to M = 2048: 9.8-10.6 vs 13.2-13.5,
+  //    fused q/k/v at M <= 384: 10.9-11.3 vs 14.1-14.7, down_proj at M = 384 / 512: 24.9 / 25.5 vs 32.0;
+  //  * beyond that the cta_group::2 kernel from 40 pair tiles on (down_proj at M = 768 / 1024: 27.2 / 28.3 us against 33.0 / 33.4
+  //    for the 256-wide single-CTA kernel; a tie elsewhere), the single-CTA kernel below that.
+  const int64_t tiles128 = ((M + 127) / 128) * ((N + 127) / 128);
   const int64_t ptiles = ((M + 255) / 256) * ((N + 255) / 256);
-  const bool use_pair = o.gemm_pair >= 0 ? o.gemm_pair != 0 : ptiles >= sms / 2;
+  const bool one_wave_128 = o.gemm_pair < 0 && o.gemm_bn == 0 && tiles128 <= sms;
+  const bool use_pair = o.gemm_pair >= 0 ? o.gemm_pair != 0 : (!one_wave_128 && ptiles >= 40);
   if (use_pair) return launch_gemm_pair(a, b, sfa, sfb, (int)M, (int)N, (int)K, alpha, alpha_dev, col_scale_dev, 0, d, ldd, st, col_bias_dev);
   GemmParams p{(const uint8_t *)sfa, (const uint8_t *)sfb, (__nv_bfloat16 *)d, alpha_dev, col_scale_dev, alpha,
                (int)M, (int)N, (int)K, ldd, 0, 0, (const __nv_bfloat16 *)col_bias_dev};
@@ -428,7 +435,7 @@ extern "C" int arcq_gemm_nvfp4_ex2(const void *a, const void *b, const void *sfa
   int bn = o.gemm_bn;
   if (bn != 128 && bn != 256) {
     // wide tiles halve A re-reads and MMA issue count; narrow tiles fill the SMs for small problems
-    bn = (tiles256 >= 2 * (int64_t)sms || N % 256 == 0) && N > 128 ? 256 : 128;
+    bn = one_wave_128 ? 128 : ((tiles256 >= 2 * (int64_t)sms || N % 256 == 0) && N > 128 ? 256 : 128);
   }
   if (bn == 256) return launch_gemm<256, 4, 16>(a, b, p, st);
   return launch_gemm<128, 5, 64>(a, b, p, st);

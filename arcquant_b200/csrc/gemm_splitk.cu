@@ -198,6 +198,9 @@ int splitk_choice(int M, int N, int K) {
   if (M > 8 * kTM) return 0;
   const int tiles = ((N + kTN - 1) / kTN) * ((M + kTM - 1) / kTM), nkb = (K + kKB - 1) / kKB;
   // (33..64 tiles with a short K: only for M <= 32, where the reduction is a few rows -- fused q/k/v at M = 8: 9.6 vs 13.6 us)
+  // (with a short K the split only pays while the reduction is a few rows: q/o at M = 128 13.1 us split against ~9.9 us for one
+  // 128-wide tile per CTA, profiles/r2_midm_kernel_choice_ab.log; down_proj's long K keeps its split up to M = 256)
+  if (nkb < 32 && M > 64) return 0;
   const int max_s = tiles <= 32 ? 8 : (tiles <= 64 && (nkb >= 32 || M <= 32) ? 4 : 1);
   int S = 1;
   while (S * 2 <= max_s && nkb / (S * 2) >= 2) S *= 2;
